@@ -1,0 +1,334 @@
+// Row-wise / element-wise kernels around the GEMMs: LayerNorm fwd+bwd, epilogue backward (dropout mask + ELU'),
+// deterministic column sums (bias / LayerNorm-affine gradients), atom featurisation, token residuals, AdamW.
+// All of these are HBM-bound streaming kernels: coalesced row-major access, one pass over the data where possible,
+// two-stage fixed-order reductions instead of atomics.
+#include "common.cuh"
+
+namespace grappa {
+
+// ------------------------------------------------------------------------------------------- LayerNorm --------
+
+constexpr float kLnEps = 1e-5f;
+
+// one warp per row; the row (<= 8 KB) stays L1-resident across the three passes
+__global__ void __launch_bounds__(256) layernorm_fwd_kernel(int64_t M, int D, const float* __restrict__ X, int64_t ldx,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            float* __restrict__ Y, int64_t ldy, float* __restrict__ mean,
+                                                            float* __restrict__ rstd) {
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= M) return;
+    const float* x = X + row * ldx;
+    float s = 0.f;
+    for (int i = lane; i < D; i += 32) s += x[i];
+    const float mu = warp_sum(s) / (float)D;
+    float v = 0.f;
+    for (int i = lane; i < D; i += 32) { const float d = x[i] - mu; v = fmaf(d, d, v); }
+    const float rs = rsqrtf(warp_sum(v) / (float)D + kLnEps);
+    float* y = Y + row * ldy;
+    for (int i = lane; i < D; i += 32) y[i] = (x[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
+    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+}
+
+__global__ void __launch_bounds__(256) layernorm_bwd_dx_kernel(int64_t M, int D, const float* __restrict__ dY, int64_t lddy,
+                                                               const float* __restrict__ X, int64_t ldx,
+                                                               const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                               const float* __restrict__ rstd, float* __restrict__ dX,
+                                                               int64_t lddx) {
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= M) return;
+    const float* x = X + row * ldx;
+    const float* dy = dY + row * lddy;
+    const float mu = mean[row], rs = rstd[row];
+    float s1 = 0.f, s2 = 0.f;
+    for (int i = lane; i < D; i += 32) {
+        const float g = dy[i] * __ldg(gamma + i);
+        s1 += g;
+        s2 = fmaf(g, (x[i] - mu) * rs, s2);
+    }
+    s1 = warp_sum(s1) / (float)D;
+    s2 = warp_sum(s2) / (float)D;
+    float* dx = dX + row * lddx;
+    for (int i = lane; i < D; i += 32) {
+        const float g = dy[i] * __ldg(gamma + i);
+        dx[i] = rs * (g - s1 - (x[i] - mu) * rs * s2);
+    }
+}
+
+// Column reductions, stage 1: CTA (32 columns x 8 row-lanes) reduces a chunk of kRowsPerChunk rows.
+constexpr int kRowsPerChunk = 256;
+
+// MODE 0: out0 = sum_rows X.   MODE 1: out0 = sum_rows dY * xhat (dgamma), out1 = sum_rows dY (dbeta).
+template <int MODE>
+__global__ void __launch_bounds__(256) colreduce_stage1_kernel(int64_t M, int64_t N, const float* __restrict__ X, int64_t ldx,
+                                                               const float* __restrict__ X2, int64_t ldx2,
+                                                               const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                               float* __restrict__ part0, float* __restrict__ part1) {
+    __shared__ float sh0[8][33];
+    __shared__ float sh1[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t col = (int64_t)blockIdx.x * 32 + tx;
+    const int64_t r0 = (int64_t)blockIdx.y * kRowsPerChunk;
+    const int64_t r1 = min(M, r0 + kRowsPerChunk);
+    float a0 = 0.f, a1 = 0.f;
+    if (col < N) {
+        for (int64_t r = r0 + ty; r < r1; r += 8) {
+            const float v = X[r * ldx + col];
+            if (MODE == 0) {
+                a0 += v;
+            } else {
+                const float xh = (X2[r * ldx2 + col] - mean[r]) * rstd[r];
+                a0 = fmaf(v, xh, a0);
+                a1 += v;
+            }
+        }
+    }
+    sh0[ty][tx] = a0;
+    if (MODE == 1) sh1[ty][tx] = a1;
+    __syncthreads();
+    if (ty == 0 && col < N) {
+        float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { s0 += sh0[j][tx]; if (MODE == 1) s1 += sh1[j][tx]; }
+        part0[(int64_t)blockIdx.y * N + col] = s0;
+        if (MODE == 1) part1[(int64_t)blockIdx.y * N + col] = s1;
+    }
+}
+
+__global__ void colreduce_stage2_kernel(int64_t R, int64_t N, const float* __restrict__ part, float* __restrict__ out) {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= N) return;
+    float s = 0.f;
+    for (int64_t r = 0; r < R; ++r) s += part[r * N + col];
+    out[col] = s;
+}
+
+// ------------------------------------------------------------------------------------- epilogue backward ------
+
+__global__ void epilogue_bwd_kernel(int64_t M, int64_t N, const float* __restrict__ dY, int64_t lddy,
+                                    const float* __restrict__ Y, int64_t ldy, const float* __restrict__ res1, int64_t ldr1,
+                                    const float* __restrict__ res2, int64_t ldr2, int act, float drop_p, uint64_t seed0,
+                                    const uint64_t* __restrict__ seed_dev, float* __restrict__ dZ, int64_t lddz) {
+    const uint64_t seed = seed0 + ((drop_p > 0.f && seed_dev) ? *seed_dev : 0ull);
+    const int64_t total = M * N;
+    const float scale = 1.0f / (1.0f - drop_p);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t m = i / N, n = i % N;
+        float g = dY[m * lddy + n];
+        bool keep = true;
+        if (drop_p > 0.f) {
+            keep = hash_uniform(seed, (uint64_t)i) >= drop_p;
+            g = keep ? g * scale : 0.f;
+        }
+        if (act == 1 && keep) {
+            float a = Y[m * ldy + n];
+            if (res1) a -= res1[m * ldr1 + n];
+            if (res2) a -= res2[m * ldr2 + n];
+            if (drop_p > 0.f) a *= (1.0f - drop_p);
+            g *= (a > 0.f) ? 1.0f : (a + 1.0f);
+        }
+        dZ[m * lddz + n] = g;
+    }
+}
+
+// ------------------------------------------------------------------------------------------- featurize --------
+
+struct FeatBlocks {
+    const float* ptr[8];
+    int width[8];
+    int ld[8];
+    int start[9];
+    int n;
+};
+
+__global__ void featurize_kernel(int64_t n_atoms, FeatBlocks fb, const float* __restrict__ charge, float* __restrict__ out,
+                                 int64_t ldo) {
+    const int W = fb.start[fb.n] + 16;
+    const int64_t total = n_atoms * W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t a = i / W;
+        const int c = (int)(i % W);
+        float v = 0.f;
+        if (c < fb.start[fb.n]) {
+            int b = 0;
+            while (c >= fb.start[b + 1]) ++b;
+            if (fb.ptr[b]) v = fb.ptr[b][a * fb.ld[b] + (c - fb.start[b])];
+        } else {
+            // ChargeEncoding (graph_attention.py:446-464): clamp to [-2,2], normalise to [0,1], 15 bins
+            const float q = fminf(fmaxf(charge[a], -2.f), 2.f);
+            const float nv = (q + 2.f) / 4.f;
+            const int j = c - fb.start[fb.n];
+            if (j == 0) {
+                v = nv;
+            } else {
+                int bin = (int)floorf(nv * 15.f);
+                bin = min(max(bin, 0), 14);
+                v = (j - 1 == bin) ? 1.f : 0.f;
+            }
+        }
+        out[a * ldo + c] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------- token residual ---------
+
+__global__ void token_residual_kernel(int64_t M, int W, int F, const float* __restrict__ X3, const float* __restrict__ X,
+                                      float* __restrict__ R) {
+    const int64_t total = M * W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % W);
+        const float x = X[i];
+        R[i] = X3[i] + (c < F ? x + x : x);
+    }
+}
+
+__global__ void token_residual_bwd_kernel(int64_t M, int W, int F, const float* __restrict__ dR, float* __restrict__ dX) {
+    const int64_t total = M * W;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int c = (int)(i % W);
+        const float g = dR[i];
+        dX[i] = c < F ? g + g : g;
+    }
+}
+
+// ----------------------------------------------------------------------------------------------- AdamW --------
+
+__global__ void adamw_kernel(int64_t n, float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                             float* __restrict__ v, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2_sqrt,
+                             float gscale) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float gi = g[i] * gscale;
+        float pi = p[i];
+        pi *= (1.0f - lr * wd);
+        const float mi = b1 * m[i] + (1.0f - b1) * gi;
+        const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2_sqrt + eps;
+        p[i] = pi - (lr / bc1) * (mi / denom);
+    }
+}
+
+static inline unsigned grid_for(int64_t n, int threads = 256, int64_t cap = 148 * 16) {
+    return (unsigned)std::max<int64_t>(1, std::min<int64_t>(cap, ceil_div(n, threads)));
+}
+
+}  // namespace grappa
+
+using namespace grappa;
+
+extern "C" int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_t ldx, const float* gamma, const float* beta,
+                                    float* Y, int64_t ldy, float* mean, float* rstd, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && D > 0 && D <= (1 << 20), "bad sizes");
+    if (M == 0) return 0;
+    GRAPPA_CHECK_ARG(X && gamma && beta && Y && mean && rstd, "null pointer");
+    layernorm_fwd_kernel<<<(unsigned)ceil_div(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(M, (int)D, X, ldx, gamma, beta, Y, ldy, mean, rstd);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D) { return 2 * ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk) * D; }
+
+extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64_t lddy, const float* X, int64_t ldx,
+                                    const float* gamma, const float* mean, const float* rstd,
+                                    float* dX, int64_t lddx, float* dgamma, float* dbeta, float* scratch, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && D > 0, "bad sizes");
+    GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && dX, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (M > 0) {
+        layernorm_bwd_dx_kernel<<<(unsigned)ceil_div(M * 32, 256), 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
+        GRAPPA_CHECK_LAUNCH();
+    }
+    if (dgamma || dbeta) {
+        GRAPPA_CHECK_ARG(dgamma && dbeta && scratch, "dgamma, dbeta and scratch must be given together");
+        const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
+        float* p0 = scratch;
+        float* p1 = scratch + R * D;
+        dim3 grid((unsigned)ceil_div(D, 32), (unsigned)R);
+        colreduce_stage1_kernel<1><<<grid, 256, 0, st>>>(M, D, dY, lddy, X, ldx, mean, rstd, p0, p1);
+        GRAPPA_CHECK_LAUNCH();
+        colreduce_stage2_kernel<<<(unsigned)ceil_div(D, 128), 128, 0, st>>>(R, D, p0, dgamma);
+        GRAPPA_CHECK_LAUNCH();
+        colreduce_stage2_kernel<<<(unsigned)ceil_div(D, 128), 128, 0, st>>>(R, D, p1, dbeta);
+        GRAPPA_CHECK_LAUNCH();
+    }
+    return 0;
+}
+
+extern "C" int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N) { return ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk) * N; }
+
+extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && N > 0, "bad sizes");
+    GRAPPA_CHECK_ARG(X && out && scratch, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
+    GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
+    dim3 grid((unsigned)ceil_div(N, 32), (unsigned)R);
+    colreduce_stage1_kernel<0><<<grid, 256, 0, st>>>(M, N, X, ldx, nullptr, 0, nullptr, nullptr, scratch, nullptr);
+    GRAPPA_CHECK_LAUNCH();
+    colreduce_stage2_kernel<<<(unsigned)ceil_div(N, 128), 128, 0, st>>>(R, N, scratch, out);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,
+                                   const float* res1, int64_t ldr1, const float* res2, int64_t ldr2, int act,
+                                   float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && N >= 0, "bad sizes");
+    GRAPPA_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "drop_p must be in [0,1)");
+    if (M * N == 0) return 0;
+    GRAPPA_CHECK_ARG(dY && dZ && (act == 0 || Y), "null pointer");
+    epilogue_bwd_kernel<<<grid_for(M * N), 256, 0, (cudaStream_t)stream>>>(M, N, dY, lddy, Y, ldy, res1, ldr1, res2, ldr2, act, drop_p, seed, seed_dev, dZ, lddz);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_featurize(int64_t n_atoms, int n_blocks, const float* const* block_ptr, const int32_t* block_width,
+                                const int32_t* block_ld, const float* charge, float* out, int64_t ldo, void* stream) {
+    GRAPPA_CHECK_ARG(n_blocks >= 0 && n_blocks <= 8, "at most 8 feature blocks");
+    GRAPPA_CHECK_ARG(n_atoms >= 0, "bad size");
+    if (n_atoms == 0) return 0;
+    GRAPPA_CHECK_ARG(charge && out, "null pointer");
+    FeatBlocks fb;
+    fb.n = n_blocks;
+    fb.start[0] = 0;
+    for (int i = 0; i < 8; ++i) {
+        fb.ptr[i] = i < n_blocks ? block_ptr[i] : nullptr;
+        fb.width[i] = i < n_blocks ? block_width[i] : 0;
+        fb.ld[i] = i < n_blocks ? block_ld[i] : 0;
+        fb.start[i + 1] = fb.start[i] + fb.width[i];
+    }
+    GRAPPA_CHECK_ARG(ldo >= fb.start[n_blocks] + 16, "output leading dimension too small");
+    featurize_kernel<<<grid_for(n_atoms * (fb.start[n_blocks] + 16)), 256, 0, (cudaStream_t)stream>>>(n_atoms, fb, charge, out, ldo);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, float* R, void* stream) {
+    if (M == 0) return 0;
+    GRAPPA_CHECK_ARG(X3 && X && R && W > 0, "bad arguments");
+    token_residual_kernel<<<grid_for(M * W), 256, 0, (cudaStream_t)stream>>>(M, W, F, X3, X, R);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_token_residual_bwd(int64_t M, int W, int F, const float* dR, float* dX, void* stream) {
+    if (M == 0) return 0;
+    GRAPPA_CHECK_ARG(dR && dX && W > 0, "bad arguments");
+    token_residual_bwd_kernel<<<grid_for(M * W), 256, 0, (cudaStream_t)stream>>>(M, W, F, dR, dX);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_adamw(int64_t n, float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                            float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                            void* stream) {
+    if (n == 0) return 0;
+    GRAPPA_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && step >= 1, "bad arguments");
+    const float bc1 = 1.0f - powf(beta1, (float)step);
+    const float bc2 = 1.0f - powf(beta2, (float)step);
+    adamw_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(n, param, grad, exp_avg, exp_avg_sq, lr, beta1, beta2, eps,
+                                                                   weight_decay, bc1, sqrtf(bc2), grad_scale);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}

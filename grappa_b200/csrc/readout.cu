@@ -1,0 +1,448 @@
+// K3 building blocks of the interaction readout (everything between the dense projections):
+// tuple gather (+ positional-encoding column) and its pull-style backward, self-attention over the <= 4 tokens of a
+// tuple in registers, permuted-view construction for the symmetriser, and the permutation sum fused with the
+// physical range maps.  Token layout is tuple-major (T, n_seq, W): a tuple's tokens are contiguous, so the identity
+// permutation of the symmetriser input is the token buffer itself.
+#include "common.cuh"
+
+namespace grappa {
+
+// ------------------------------------------------------------------------------------------ tuple gather ------
+
+// one thread per float4 of X; requires W % 4 == 0 and lda % 4 == 0
+__global__ void tuple_gather_fwd_kernel(int64_t rows, int n_seq, int F, int W, const float* __restrict__ A, int64_t lda,
+                                        const int32_t* __restrict__ idx, const float* __restrict__ pe, float* __restrict__ X) {
+    const int W4 = W / 4;
+    const int64_t total = rows * W4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / W4;
+        const int c = (int)(i % W4) * 4;
+        const int64_t a = __ldg(idx + r);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < F) v = __ldg(reinterpret_cast<const float4*>(A + a * lda + c));
+        if (c + 3 >= F) {
+            const float pv = pe ? __ldg(pe + (r % n_seq)) : 0.f;
+            if (c + 0 >= F) v.x = pv;
+            if (c + 1 >= F) v.y = pv;
+            if (c + 2 >= F) v.z = pv;
+            if (c + 3 >= F) v.w = pv;
+        }
+        reinterpret_cast<float4*>(X)[i] = v;
+    }
+}
+
+// one warp per atom: dA[a, 0:F] = sum over incident token rows of dX[row, 0:F]; columns >= F of dA are zeroed
+__global__ void __launch_bounds__(256) tuple_gather_bwd_kernel(int64_t N, int F, int W, const float* __restrict__ dX,
+                                                               const int32_t* __restrict__ inc_ptr, const int32_t* __restrict__ inc_tok,
+                                                               float* __restrict__ dA, int64_t ldda) {
+    const int64_t a = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (a >= N) return;
+    const int W4 = W / 4;
+    const int q0 = __ldg(inc_ptr + a), q1 = __ldg(inc_ptr + a + 1);
+    for (int c4 = lane; c4 < W4; c4 += 32) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = q0; q < q1; ++q) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(dX + (int64_t)__ldg(inc_tok + q) * W) + c4);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        const int c = c4 * 4;
+        if (c + 0 >= F) s.x = 0.f;
+        if (c + 1 >= F) s.y = 0.f;
+        if (c + 2 >= F) s.z = 0.f;
+        if (c + 3 >= F) s.w = 0.f;
+        *reinterpret_cast<float4*>(dA + a * ldda + c) = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ tuple attention ---
+
+__device__ __forceinline__ float sum8(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+__device__ __forceinline__ float dot8(const float4 (&a)[2], const float4 (&b)[2]) {
+    return a[0].x * b[0].x + a[0].y * b[0].y + a[0].z * b[0].z + a[0].w * b[0].w +
+           a[1].x * b[1].x + a[1].y * b[1].y + a[1].z * b[1].z + a[1].w * b[1].w;
+}
+__device__ __forceinline__ void axpy8(float s, const float4 (&x)[2], float4 (&y)[2]) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r) { y[r].x = fmaf(s, x[r].x, y[r].x); y[r].y = fmaf(s, x[r].y, y[r].y); y[r].z = fmaf(s, x[r].z, y[r].z); y[r].w = fmaf(s, x[r].w, y[r].w); }
+}
+
+// head_dim 64: 8 lanes per head, each lane holds float4 #sub and #(sub+8) of the head's 16 float4s.
+// One warp handles 4 heads of one tuple.
+template <int S>
+__global__ void __launch_bounds__(128) tuple_attn_fwd_kernel(int64_t T, int n_heads, const float* __restrict__ qkv,
+                                                             float* __restrict__ out) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int groups = n_heads / 4;
+    if (w >= T * groups) return;
+    const int64_t t = w / groups;
+    const int head = (int)(w % groups) * 4 + lane / 8;
+    const int sub = lane % 8;
+    const int E = n_heads * 64;
+    float4 q[S][2], k[S][2], v[S][2];
+#pragma unroll
+    for (int j = 0; j < S; ++j) {
+        const float4* row = reinterpret_cast<const float4*>(qkv + (t * S + j) * 3 * E + head * 64);
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            q[j][r] = __ldg(row + sub + 8 * r);
+            k[j][r] = __ldg(row + E / 4 + sub + 8 * r);
+            v[j][r] = __ldg(row + 2 * (E / 4) + sub + 8 * r);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        float s[S], mx = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < S; ++j) { s[j] = sum8(dot8(q[i], k[j])) * 0.125f; mx = fmaxf(mx, s[j]); }
+        float den = 0.f;
+#pragma unroll
+        for (int j = 0; j < S; ++j) { s[j] = expf(s[j] - mx); den += s[j]; }
+        const float inv = 1.0f / den;
+        float4 o[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+#pragma unroll
+        for (int j = 0; j < S; ++j) axpy8(s[j] * inv, v[j], o);
+        float4* orow = reinterpret_cast<float4*>(out + (t * S + i) * E + head * 64);
+        orow[sub] = o[0];
+        orow[sub + 8] = o[1];
+    }
+}
+
+template <int S>
+__global__ void __launch_bounds__(128) tuple_attn_bwd_kernel(int64_t T, int n_heads, const float* __restrict__ qkv,
+                                                             const float* __restrict__ dOut, float* __restrict__ dqkv) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int groups = n_heads / 4;
+    if (w >= T * groups) return;
+    const int64_t t = w / groups;
+    const int head = (int)(w % groups) * 4 + lane / 8;
+    const int sub = lane % 8;
+    const int E = n_heads * 64;
+    float4 q[S][2], k[S][2], v[S][2], g[S][2];
+#pragma unroll
+    for (int j = 0; j < S; ++j) {
+        const float4* row = reinterpret_cast<const float4*>(qkv + (t * S + j) * 3 * E + head * 64);
+        const float4* grow = reinterpret_cast<const float4*>(dOut + (t * S + j) * E + head * 64);
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            q[j][r] = __ldg(row + sub + 8 * r);
+            k[j][r] = __ldg(row + E / 4 + sub + 8 * r);
+            v[j][r] = __ldg(row + 2 * (E / 4) + sub + 8 * r);
+            g[j][r] = __ldg(grow + sub + 8 * r);
+        }
+    }
+    float P[S][S], dS[S][S];
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        float mx = -INFINITY, den = 0.f;
+#pragma unroll
+        for (int j = 0; j < S; ++j) { P[i][j] = sum8(dot8(q[i], k[j])) * 0.125f; mx = fmaxf(mx, P[i][j]); }
+#pragma unroll
+        for (int j = 0; j < S; ++j) { P[i][j] = expf(P[i][j] - mx); den += P[i][j]; }
+        const float inv = 1.0f / den;
+        float dsum = 0.f;
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            P[i][j] *= inv;
+            dS[i][j] = sum8(dot8(g[i], v[j]));       // dP_ij
+            dsum = fmaf(P[i][j], dS[i][j], dsum);
+        }
+#pragma unroll
+        for (int j = 0; j < S; ++j) dS[i][j] = P[i][j] * (dS[i][j] - dsum) * 0.125f;   // includes the 1/sqrt(64) scale
+    }
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        float4 dq[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+        float4 dk[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+        float4 dv[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            axpy8(dS[i][j], k[j], dq);      // dq_i = sum_j dS_ij k_j
+            axpy8(dS[j][i], q[j], dk);      // dk_i = sum_j dS_ji q_j
+            axpy8(P[j][i], g[j], dv);       // dv_i = sum_j P_ji dO_j
+        }
+        float4* orow = reinterpret_cast<float4*>(dqkv + (t * S + i) * 3 * E + head * 64);
+        orow[sub] = dq[0]; orow[sub + 8] = dq[1];
+        orow[E / 4 + sub] = dk[0]; orow[E / 4 + sub + 8] = dk[1];
+        orow[2 * (E / 4) + sub] = dv[0]; orow[2 * (E / 4) + sub + 8] = dv[1];
+    }
+}
+
+// ------------------------------------------------------------------------------------------ symmetriser -------
+
+struct PermTable {
+    int perm[6][4];
+    int inv[6][4];
+    float pref[6];
+};
+
+__global__ void symm_permute_fwd_kernel(int64_t T, int n_seq, int W, int P, PermTable pt, const float* __restrict__ X,
+                                        float* __restrict__ Y) {
+    const int W4 = W / 4;
+    const int64_t row4 = (int64_t)n_seq * W4;
+    const int64_t total = (int64_t)P * T * row4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / row4;
+        const int rem = (int)(i % row4);
+        const int pos = rem / W4, c4 = rem % W4;
+        const int p = (int)(row / T);
+        const int64_t t = row % T;
+        reinterpret_cast<float4*>(Y)[i] = __ldg(reinterpret_cast<const float4*>(X) + (t * n_seq + pt.perm[p][pos]) * W4 + c4);
+    }
+}
+
+__global__ void symm_permute_bwd_kernel(int64_t T, int n_seq, int W, int P, PermTable pt, const float* __restrict__ dY,
+                                        float* __restrict__ dX) {
+    const int W4 = W / 4;
+    const int64_t row4 = (int64_t)n_seq * W4;
+    const int64_t total = T * row4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = i / row4;
+        const int rem = (int)(i % row4);
+        const int j = rem / W4, c4 = rem % W4;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int p = 0; p < P; ++p) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(dY) + ((int64_t)p * T + t) * row4 + pt.inv[p][j] * W4 + c4);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        reinterpret_cast<float4*>(dX)[i] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ finalize ----------
+
+struct FinalizeConsts {
+    float eq_a, eq_b, eq_c, k_mos, k_std, k_min, cutoff;
+    float pref[6];
+};
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float to_positive(float c, float mos, float sd, float mn) { return sd * (elu1(mos + c - 1.0f) + 1.0f) + mn; }
+__device__ __forceinline__ float to_positive_grad(float c, float mos, float sd) { const float z = mos + c - 1.0f; return sd * (z > 0.f ? 1.0f : expf(z)); }
+
+constexpr int kMaxOut = 12;
+
+__global__ void readout_finalize_fwd_kernel(int kind, int64_t T, int P, int n_out, const float* __restrict__ S, FinalizeConsts fc,
+                                            const float* __restrict__ kstd, const float* __restrict__ kmean, int n_per, int col0,
+                                            float* __restrict__ C, float* __restrict__ eq, float* __restrict__ k) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    float c[kMaxOut];
+#pragma unroll
+    for (int j = 0; j < kMaxOut; ++j) {
+        c[j] = 0.f;
+        if (j < n_out) {
+            for (int p = 0; p < P; ++p) c[j] += fc.pref[p] * S[((int64_t)p * T + t) * n_out + j];
+            C[t * n_out + j] = c[j];
+        }
+    }
+    if (kind == 0) {
+        eq[t] = to_positive(c[0], fc.eq_a, fc.eq_b, fc.eq_c);
+        k[t] = to_positive(c[1], fc.k_mos, fc.k_std, fc.k_min);
+    } else if (kind == 1) {
+        eq[t] = fc.eq_b * sigmoidf_(fc.eq_a * c[0]);
+        k[t] = to_positive(c[1], fc.k_mos, fc.k_std, fc.k_min);
+    } else {
+        const int nh = kind == 2 ? n_out / 2 : n_out;
+        for (int j = 0; j < n_per; ++j) k[t * n_per + j] = 0.f;
+#pragma unroll
+        for (int j = 0; j < kMaxOut / 2; ++j) {
+            if (j < nh) {
+                float v = kind == 2 ? c[j] * sigmoidf_(c[nh + j]) * kstd[j] : c[j] * kstd[j] + kmean[j];
+                if (fc.cutoff > 0.f && !(fabsf(v) > fc.cutoff)) v = 0.f;
+                k[t * n_per + col0 + j] = v;
+            }
+        }
+    }
+}
+
+__global__ void readout_finalize_bwd_kernel(int kind, int64_t T, int P, int n_out, const float* __restrict__ C, FinalizeConsts fc,
+                                            const float* __restrict__ kstd, const float* __restrict__ kmean, int n_per, int col0,
+                                            const float* __restrict__ d_eq, const float* __restrict__ d_k, float* __restrict__ dS) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= T) return;
+    float c[kMaxOut], dc[kMaxOut];
+#pragma unroll
+    for (int j = 0; j < kMaxOut; ++j) { c[j] = j < n_out ? C[t * n_out + j] : 0.f; dc[j] = 0.f; }
+    if (kind == 0) {
+        dc[0] = (d_eq ? d_eq[t] : 0.f) * to_positive_grad(c[0], fc.eq_a, fc.eq_b);
+        dc[1] = (d_k ? d_k[t] : 0.f) * to_positive_grad(c[1], fc.k_mos, fc.k_std);
+    } else if (kind == 1) {
+        const float s = sigmoidf_(fc.eq_a * c[0]);
+        dc[0] = (d_eq ? d_eq[t] : 0.f) * fc.eq_b * fc.eq_a * s * (1.0f - s);
+        dc[1] = (d_k ? d_k[t] : 0.f) * to_positive_grad(c[1], fc.k_mos, fc.k_std);
+    } else {
+        const int nh = kind == 2 ? n_out / 2 : n_out;
+#pragma unroll
+        for (int j = 0; j < kMaxOut / 2; ++j) {
+            if (j < nh) {
+                const float g = d_k ? d_k[t * n_per + col0 + j] : 0.f;
+                if (kind == 2) {
+                    const float s = sigmoidf_(c[nh + j]);
+                    const float v = c[j] * s * kstd[j];
+                    const bool pass = !(fc.cutoff > 0.f) || fabsf(v) > fc.cutoff;
+                    dc[j] = pass ? g * s * kstd[j] : 0.f;
+                    dc[nh + j] = pass ? g * c[j] * s * (1.0f - s) * kstd[j] : 0.f;
+                } else {
+                    const float v = c[j] * kstd[j] + kmean[j];
+                    const bool pass = !(fc.cutoff > 0.f) || fabsf(v) > fc.cutoff;
+                    dc[j] = pass ? g * kstd[j] : 0.f;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kMaxOut; ++j)
+        if (j < n_out)
+            for (int p = 0; p < P; ++p) dS[((int64_t)p * T + t) * n_out + j] = fc.pref[p] * dc[j];
+}
+
+static inline unsigned grid_for(int64_t n, int threads = 256, int64_t cap = 148 * 16) {
+    return (unsigned)std::max<int64_t>(1, std::min<int64_t>(cap, ceil_div(n, threads)));
+}
+
+static int make_perm_table(int n_seq, int P, const int32_t* perm, PermTable& pt) {
+    GRAPPA_CHECK_ARG(P >= 1 && P <= 6 && n_seq >= 1 && n_seq <= 4 && perm, "need 1..6 permutations of 1..4 positions");
+    for (int p = 0; p < P; ++p) {
+        bool seen[4] = {false, false, false, false};
+        for (int i = 0; i < n_seq; ++i) {
+            const int j = perm[p * n_seq + i];
+            GRAPPA_CHECK_ARG(j >= 0 && j < n_seq && !seen[j], "invalid permutation");
+            seen[j] = true;
+            pt.perm[p][i] = j;
+            pt.inv[p][j] = i;
+        }
+    }
+    return 0;
+}
+
+static int make_consts(int P, const float* prefactor, const float* consts, FinalizeConsts& fc) {
+    GRAPPA_CHECK_ARG(P >= 1 && P <= 6 && prefactor && consts, "bad prefactor/consts");
+    fc.eq_a = consts[0]; fc.eq_b = consts[1]; fc.eq_c = consts[2]; fc.k_mos = consts[3]; fc.k_std = consts[4];
+    fc.k_min = consts[5]; fc.cutoff = consts[6];
+    for (int p = 0; p < 6; ++p) fc.pref[p] = p < P ? prefactor[p] : 0.f;
+    return 0;
+}
+
+}  // namespace grappa
+
+using namespace grappa;
+
+extern "C" int grappa_tuple_gather_fwd(int64_t T, int n_seq, int F, int W, const float* A, int64_t lda, const int32_t* idx,
+                                       const float* pe, float* X, void* stream) {
+    GRAPPA_CHECK_ARG(T >= 0 && n_seq >= 1 && n_seq <= 4 && F > 0 && F <= W, "bad sizes");
+    GRAPPA_CHECK_ARG(W % 4 == 0 && lda % 4 == 0 && lda >= ((F + 3) / 4) * 4, "W and lda must be multiples of 4 (lda >= F rounded up)");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(A && idx && X, "null pointer");
+    tuple_gather_fwd_kernel<<<grid_for(T * n_seq * (W / 4)), 256, 0, (cudaStream_t)stream>>>(T * n_seq, n_seq, F, W, A, lda, idx, pe, X);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_tuple_gather_bwd(int64_t N, int F, int W, const float* dX, const int32_t* inc_ptr, const int32_t* inc_tok,
+                                       float* dA, int64_t ldda, void* stream) {
+    GRAPPA_CHECK_ARG(N >= 0 && F > 0 && F <= W && W % 4 == 0 && ldda % 4 == 0 && ldda >= W, "bad sizes");
+    if (N == 0) return 0;
+    GRAPPA_CHECK_ARG(inc_ptr && inc_tok && dA, "null pointer");
+    tuple_gather_bwd_kernel<<<(unsigned)ceil_div(N * 32, 256), 256, 0, (cudaStream_t)stream>>>(N, F, W, dX, inc_ptr, inc_tok, dA, ldda);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, float* out, void* stream) {
+    GRAPPA_CHECK_ARG(head_dim == 64 && n_heads % 4 == 0 && n_heads > 0, "tuple attention needs head_dim 64 and n_heads % 4 == 0");
+    GRAPPA_CHECK_ARG(n_seq >= 1 && n_seq <= 4 && T >= 0, "n_seq must be 1..4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(qkv && out, "null pointer");
+    const int64_t warps = T * (n_heads / 4);
+    const unsigned grid = (unsigned)ceil_div(warps * 32, 128);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (n_seq) {
+        case 1: tuple_attn_fwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
+        case 2: tuple_attn_fwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
+        case 3: tuple_attn_fwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
+        default: tuple_attn_fwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
+    }
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const float* dOut,
+                                     float* dqkv, void* stream) {
+    GRAPPA_CHECK_ARG(head_dim == 64 && n_heads % 4 == 0 && n_heads > 0, "tuple attention needs head_dim 64 and n_heads % 4 == 0");
+    GRAPPA_CHECK_ARG(n_seq >= 1 && n_seq <= 4 && T >= 0, "n_seq must be 1..4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(qkv && dOut && dqkv, "null pointer");
+    const int64_t warps = T * (n_heads / 4);
+    const unsigned grid = (unsigned)ceil_div(warps * 32, 128);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (n_seq) {
+        case 1: tuple_attn_bwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
+        case 2: tuple_attn_bwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
+        case 3: tuple_attn_bwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
+        default: tuple_attn_bwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
+    }
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_symm_permute_fwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* X, float* Y, void* stream) {
+    PermTable pt;
+    if (int rc = make_perm_table(n_seq, P, perm, pt)) return rc;
+    GRAPPA_CHECK_ARG(T >= 0 && W > 0 && W % 4 == 0, "W must be a multiple of 4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(X && Y, "null pointer");
+    symm_permute_fwd_kernel<<<grid_for((int64_t)P * T * n_seq * (W / 4)), 256, 0, (cudaStream_t)stream>>>(T, n_seq, W, P, pt, X, Y);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_symm_permute_bwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* dY, float* dX, void* stream) {
+    PermTable pt;
+    if (int rc = make_perm_table(n_seq, P, perm, pt)) return rc;
+    GRAPPA_CHECK_ARG(T >= 0 && W > 0 && W % 4 == 0, "W must be a multiple of 4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(dY && dX, "null pointer");
+    symm_permute_bwd_kernel<<<grid_for(T * n_seq * (W / 4)), 256, 0, (cudaStream_t)stream>>>(T, n_seq, W, P, pt, dY, dX);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_readout_finalize_fwd(int kind, int64_t T, int P, int n_out, const float* S, const float* prefactor,
+                                           const float* consts, const float* kstd, const float* kmean, int n_per, int col0,
+                                           float* C, float* eq, float* k, void* stream) {
+    GRAPPA_CHECK_ARG(kind >= 0 && kind <= 3 && n_out >= 1 && n_out <= kMaxOut, "bad kind / n_out");
+    FinalizeConsts fc;
+    if (int rc = make_consts(P, prefactor, consts, fc)) return rc;
+    if (kind <= 1) GRAPPA_CHECK_ARG(n_out >= 2 && eq, "harmonic writers need n_out >= 2 and an eq output");
+    if (kind >= 2) {
+        const int nh = kind == 2 ? n_out / 2 : n_out;
+        GRAPPA_CHECK_ARG(kstd && (kind == 2 || kmean) && (kind != 2 || n_out % 2 == 0), "torsion writer needs k_std (and k_mean when ungated)");
+        GRAPPA_CHECK_ARG(col0 >= 0 && col0 + nh <= n_per && nh <= kMaxOut / 2, "torsion columns out of range");
+    }
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(S && C && k, "null pointer");
+    readout_finalize_fwd_kernel<<<(unsigned)ceil_div(T, 128), 128, 0, (cudaStream_t)stream>>>(kind, T, P, n_out, S, fc, kstd, kmean, n_per, col0, C, eq, k);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_readout_finalize_bwd(int kind, int64_t T, int P, int n_out, const float* C, const float* prefactor,
+                                           const float* consts, const float* kstd, const float* kmean, int n_per, int col0,
+                                           const float* d_eq, const float* d_k, float* dS, void* stream) {
+    GRAPPA_CHECK_ARG(kind >= 0 && kind <= 3 && n_out >= 1 && n_out <= kMaxOut, "bad kind / n_out");
+    FinalizeConsts fc;
+    if (int rc = make_consts(P, prefactor, consts, fc)) return rc;
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(C && dS, "null pointer");
+    readout_finalize_bwd_kernel<<<(unsigned)ceil_div(T, 128), 128, 0, (cudaStream_t)stream>>>(kind, T, P, n_out, C, fc, kstd, kmean, n_per, col0, d_eq, d_k, dS);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}

@@ -1,0 +1,479 @@
+"""
+torch.autograd.Function wrappers around the C ABI (include/grappa_b200.h).  PyTorch supplies device memory, the
+current stream and the autograd tape; every arithmetic step is a kernel of libgrappa_b200.so.  There is no fallback:
+CPU tensors are rejected.
+"""
+import ctypes
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+
+MATH_MODE = 0          # 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm)
+ACT_NONE, ACT_ELU = 0, 1
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _req(t: torch.Tensor, name: str, dtype=torch.float32):
+    if not t.is_cuda:
+        raise _lib.GrappaKernelError(f"{name} must be a CUDA tensor (grappa_b200 has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t
+
+
+def _rows2d(t: torch.Tensor, name: str):
+    """2-D view with unit inner stride; returns (tensor, leading dimension)."""
+    _req(t, name)
+    if t.dim() != 2:
+        raise ValueError(f"{name} must be 2-D, got shape {tuple(t.shape)}")
+    if t.stride(1) != 1 or (t.shape[0] > 1 and t.stride(0) < t.shape[1]):
+        t = t.contiguous()
+    return t, (t.stride(0) if t.shape[0] > 1 else max(t.shape[1], 1))
+
+
+class DropoutSeeds:
+    """Per-process dropout seed stream.  `base` is a host counter advanced per call; `dev` is an optional device
+    uint64 that the step driver bumps between CUDA-graph replays so that replays draw fresh masks."""
+    base = 0x5EED
+    dev: Optional[torch.Tensor] = None
+
+    @classmethod
+    def next(cls) -> int:
+        cls.base = (cls.base * 6364136223846793005 + 1442695040888963407) & 0xFFFFFFFFFFFFFFFF
+        return cls.base
+
+    @classmethod
+    def manual_seed(cls, seed: int):
+        cls.base = seed & 0xFFFFFFFFFFFFFFFF
+
+
+def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
+         drop_p=0.0, seed=0, seed_dev=None):
+    _lib.check(_lib.lib().grappa_gemm(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act,
+                                      _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), MATH_MODE,
+                                      _stream()))
+
+
+class LinearFn(torch.autograd.Function):
+    """y = dropout(act(x W^T + b)) + res1 + res2, columns padded to `out_ld` (pad columns are zero)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld):
+        x, lda = _rows2d(x, "x")
+        w, ldb = _rows2d(weight, "weight")
+        M, K = x.shape
+        N = w.shape[0]
+        if w.shape[1] != K:
+            raise ValueError(f"weight {tuple(w.shape)} does not match input features {K}")
+        ldc = int(out_ld) if out_ld else N
+        y = torch.empty((M, ldc), device=x.device, dtype=torch.float32)
+        if ldc > N:
+            y[:, N:].zero_()
+        r1 = r2 = None
+        l1 = l2 = 0
+        if res1 is not None:
+            r1, l1 = _rows2d(res1, "res1")
+        if res2 is not None:
+            r2, l2 = _rows2d(res2, "res2")
+        seed = DropoutSeeds.next() if drop_p > 0 else 0
+        seed_dev = DropoutSeeds.dev if drop_p > 0 else None
+        gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev)
+        ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
+                              r2 if act != ACT_NONE else None)
+        ctx.cfg = (act, float(drop_p), seed, seed_dev, N, ldc, bias is not None, res1 is not None, res2 is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y, r1, r2 = ctx.saved_tensors
+        act, drop_p, seed, seed_dev, N, ldc, has_bias, has_r1, has_r2 = ctx.cfg
+        L = _lib.lib()
+        dy, lddy = _rows2d(dy, "grad")
+        M, K = x.shape
+        lda = x.stride(0) if M > 1 else K
+        if act != ACT_NONE or drop_p > 0:
+            dz = torch.empty((M, N), device=dy.device, dtype=torch.float32)
+            _lib.check(L.grappa_epilogue_bwd(M, N, _p(dy), lddy, _p(y), ldc, _p(r1), r1.stride(0) if r1 is not None and M > 1 else ldc,
+                                             _p(r2), r2.stride(0) if r2 is not None and M > 1 else ldc, act, drop_p, seed,
+                                             _p(seed_dev), _p(dz), N, _stream()))
+            lddz = N
+        else:
+            dz, lddz = dy, lddy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
+            gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty((N, K), device=dy.device, dtype=torch.float32)
+            gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty((N,), device=dy.device, dtype=torch.float32)
+            scratch = torch.empty((int(L.grappa_colsum_scratch_floats(M, N)),), device=dy.device, dtype=torch.float32)
+            _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
+        dr = dy if ldc == N else dy[:, :N]
+        return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,
+                dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None)
+
+
+def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0):
+    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld)
+
+
+class LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta):
+        x, ldx = _rows2d(x, "x")
+        M, D = x.shape
+        y = torch.empty((M, D), device=x.device, dtype=torch.float32)
+        stats = torch.empty((2, max(M, 1)), device=x.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_layernorm_fwd(M, D, _p(x), ldx, _p(gamma), _p(beta), _p(y), D, _p(stats[0]), _p(stats[1]),
+                                                   _stream()))
+        ctx.save_for_backward(x, gamma, stats)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, stats = ctx.saved_tensors
+        L = _lib.lib()
+        dy, lddy = _rows2d(dy, "grad")
+        M, D = x.shape
+        ldx = x.stride(0) if M > 1 else D
+        dx = torch.empty((M, D), device=dy.device, dtype=torch.float32)
+        need_affine = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dg = db = scratch = None
+        if need_affine:
+            dg = torch.empty((D,), device=dy.device, dtype=torch.float32)
+            db = torch.empty((D,), device=dy.device, dtype=torch.float32)
+            scratch = torch.empty((int(L.grappa_layernorm_bwd_scratch_floats(M, D)),), device=dy.device, dtype=torch.float32)
+        _lib.check(L.grappa_layernorm_bwd(M, D, _p(dy), lddy, _p(x), ldx, _p(gamma), _p(stats[0]), _p(stats[1]), _p(dx), D,
+                                          _p(dg), _p(db), _p(scratch), _stream()))
+        return dx, dg, db
+
+
+def layer_norm(x, gamma, beta):
+    return LayerNormFn.apply(x, gamma, beta)
+
+
+def featurize(blocks, charge: torch.Tensor) -> torch.Tensor:
+    """blocks: list of (tensor or None, width).  Returns (N, sum(width) + 16) features (no gradient: inputs)."""
+    n = charge.shape[0]
+    ptrs = (ctypes.c_void_p * 8)()
+    widths = (ctypes.c_int32 * 8)()
+    lds = (ctypes.c_int32 * 8)()
+    keep = []
+    total = 0
+    for i, (t, wdt) in enumerate(blocks):
+        if t is not None:
+            t = _req(t, "feature").reshape(n, -1)
+            t, ld = _rows2d(t, "feature")
+            keep.append(t)
+            ptrs[i] = t.data_ptr()
+            lds[i] = ld
+        else:
+            ptrs[i] = None
+            lds[i] = 0
+        widths[i] = wdt
+        total += wdt
+    out = torch.empty((n, total + 16), device=charge.device, dtype=torch.float32)
+    charge = _req(charge, "partial_charge").contiguous()
+    _lib.check(_lib.lib().grappa_featurize(n, len(blocks), ptrs, widths, lds, _p(charge), _p(out), total + 16, _stream()))
+    return out
+
+
+class GnnAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ft, plan, n_heads):
+        ft, ld = _rows2d(ft, "ft")
+        if ld != ft.shape[1]:
+            ft = ft.contiguous()
+        N, HD = ft.shape
+        D = HD // n_heads
+        out = torch.empty_like(ft)
+        lse = torch.empty((N, n_heads), device=ft.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_gnn_attn_fwd(N, n_heads, D, _p(ft), plan.ptr("in_ptr"), plan.ptr("in_nbr"), _p(out), _p(lse),
+                                                  _stream()))
+        ctx.save_for_backward(ft, out, lse)
+        ctx.plan, ctx.n_heads = plan, n_heads
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        ft, out, lse = ctx.saved_tensors
+        plan, H = ctx.plan, ctx.n_heads
+        dout = dout.contiguous()
+        N, HD = ft.shape
+        delta = torch.empty((N, H), device=ft.device, dtype=torch.float32)
+        dft = torch.empty_like(ft)
+        _lib.check(_lib.lib().grappa_gnn_attn_bwd(N, H, HD // H, _p(ft), _p(out), _p(lse), _p(dout), plan.ptr("in_ptr"),
+                                                  plan.ptr("in_nbr"), plan.ptr("out_ptr"), plan.ptr("out_nbr"), _p(delta), _p(dft),
+                                                  _stream()))
+        return dft, None, None
+
+
+def gnn_attention(ft, plan, n_heads):
+    return GnnAttnFn.apply(ft, plan, n_heads)
+
+
+class TupleGatherFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, plan, level, n_seq, F, W, pe):
+        a, lda = _rows2d(a, "atom_feats")
+        T = plan.T[level]
+        x = torch.empty((T * n_seq, W), device=a.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_tuple_gather_fwd(T, n_seq, F, W, _p(a), lda, plan.ptr("idx_" + level), _p(pe), _p(x), _stream()))
+        ctx.cfg = (plan, level, F, W, a.shape[0], lda)
+        return x
+
+    @staticmethod
+    def backward(ctx, dx):
+        plan, level, F, W, N, lda = ctx.cfg
+        dx = dx.contiguous()
+        ldda = max(lda, W)
+        da = torch.empty((N, ldda), device=dx.device, dtype=torch.float32)
+        if ldda > W:
+            da[:, W:].zero_()
+        _lib.check(_lib.lib().grappa_tuple_gather_bwd(N, F, W, _p(dx), plan.ptr("inc_ptr_" + level), plan.ptr("inc_tok_" + level),
+                                                      _p(da), ldda, _stream()))
+        return da, None, None, None, None, None, None
+
+
+def tuple_gather(a, plan, level, n_seq, F, W, pe=None):
+    return TupleGatherFn.apply(a, plan, level, n_seq, F, W, pe)
+
+
+class TupleAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, T, n_seq, n_heads):
+        qkv = _req(qkv, "qkv").contiguous()
+        E = qkv.shape[1] // 3
+        out = torch.empty((T * n_seq, E), device=qkv.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_tuple_attn_fwd(T, n_seq, n_heads, E // n_heads, _p(qkv), _p(out), _stream()))
+        ctx.save_for_backward(qkv)
+        ctx.cfg = (T, n_seq, n_heads, E)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (qkv,) = ctx.saved_tensors
+        T, n_seq, n_heads, E = ctx.cfg
+        dout = dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        _lib.check(_lib.lib().grappa_tuple_attn_bwd(T, n_seq, n_heads, E // n_heads, _p(qkv), _p(dout), _p(dqkv), _stream()))
+        return dqkv, None, None, None
+
+
+def tuple_attention(qkv, T, n_seq, n_heads):
+    return TupleAttnFn.apply(qkv, T, n_seq, n_heads)
+
+
+class TokenResidualFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x3, x, F):
+        x3 = _req(x3, "x3").contiguous()
+        x = _req(x, "x").contiguous()
+        M, W = x.shape
+        r = torch.empty_like(x)
+        _lib.check(_lib.lib().grappa_token_residual(M, W, F, _p(x3), _p(x), _p(r), _stream()))
+        ctx.cfg = (M, W, F)
+        return r
+
+    @staticmethod
+    def backward(ctx, dr):
+        M, W, F = ctx.cfg
+        dr = dr.contiguous()
+        dx = None
+        if ctx.needs_input_grad[1]:
+            dx = torch.empty_like(dr)
+            _lib.check(_lib.lib().grappa_token_residual_bwd(M, W, F, _p(dr), _p(dx), _stream()))
+        return dr, dx, None
+
+
+def token_residual(x3, x, F):
+    return TokenResidualFn.apply(x3, x, F)
+
+
+class SymmPermuteFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, T, n_seq, perms):
+        x = _req(x, "x").contiguous()
+        W = x.shape[1]
+        P = len(perms)
+        flat = (ctypes.c_int32 * (P * n_seq))(*[int(v) for p in perms for v in p])
+        y = torch.empty((P * T, n_seq * W), device=x.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_symm_permute_fwd(T, n_seq, W, P, flat, _p(x), _p(y), _stream()))
+        ctx.cfg = (T, n_seq, W, P, flat)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        T, n_seq, W, P, flat = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty((T * n_seq, W), device=dy.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_symm_permute_bwd(T, n_seq, W, P, flat, _p(dy), _p(dx), _stream()))
+        return dx, None, None, None
+
+
+def symm_permute(x, T, n_seq, perms):
+    return SymmPermuteFn.apply(x, T, n_seq, perms)
+
+
+class ReadoutFinalizeFn(torch.autograd.Function):
+    """kind 0 bond / 1 angle -> (eq, k); kind 2 gated torsion / 3 ungated torsion -> k (T, n_per)."""
+
+    @staticmethod
+    def forward(ctx, s, kind, T, prefactors, consts, kstd, kmean, n_per, col0):
+        s = _req(s, "s").contiguous()
+        P = len(prefactors)
+        n_out = s.shape[1]
+        pref = (ctypes.c_float * P)(*[float(v) for v in prefactors])
+        cst = (ctypes.c_float * 8)(*([float(v) for v in consts] + [0.0] * (8 - len(consts))))
+        c = torch.empty((T, n_out), device=s.device, dtype=torch.float32)
+        if kind <= 1:
+            eq = torch.empty((T,), device=s.device, dtype=torch.float32)
+            k = torch.empty((T,), device=s.device, dtype=torch.float32)
+        else:
+            eq = None
+            k = torch.empty((T, n_per), device=s.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_readout_finalize_fwd(kind, T, P, n_out, _p(s), pref, cst, _p(kstd), _p(kmean), n_per, col0,
+                                                          _p(c), _p(eq), _p(k), _stream()))
+        ctx.save_for_backward(c, kstd, kmean)
+        ctx.cfg = (kind, T, P, n_out, pref, cst, n_per, col0)
+        if kind <= 1:
+            return eq, k
+        return k
+
+    @staticmethod
+    def backward(ctx, *grads):
+        c, kstd, kmean = ctx.saved_tensors
+        kind, T, P, n_out, pref, cst, n_per, col0 = ctx.cfg
+        if kind <= 1:
+            d_eq, d_k = grads
+        else:
+            d_eq, d_k = None, grads[0]
+        d_eq = d_eq.contiguous() if d_eq is not None else None
+        d_k = d_k.contiguous() if d_k is not None else None
+        ds = torch.empty((P * T, n_out), device=c.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_readout_finalize_bwd(kind, T, P, n_out, _p(c), pref, cst, _p(kstd), _p(kmean), n_per, col0,
+                                                          _p(d_eq), _p(d_k), _p(ds), _stream()))
+        return ds, None, None, None, None, None, None, None, None
+
+
+def readout_finalize(s, kind, T, prefactors, consts, kstd=None, kmean=None, n_per=0, col0=0):
+    return ReadoutFinalizeFn.apply(s, kind, T, prefactors, consts, kstd, kmean, n_per, col0)
+
+
+class EnergyFn(torch.autograd.Function):
+    """(k2, eq2, k3, eq3, k4, k4i, xyz) -> (energy (n_mol,C), gradient (N,C,3), term_energy (4,n_mol,C), x..., e...)."""
+
+    @staticmethod
+    def forward(ctx, k2, eq2, k3, eq3, k4, k4i, xyz, plan, term_mask, want_coords):
+        xyz = _req(xyz, "xyz").contiguous()
+        N, C, _ = xyz.shape
+        dev = xyz.device
+        T = plan.T
+
+        def prep(t, shape):
+            if t is None:
+                return torch.zeros(shape, device=dev, dtype=torch.float32)
+            return _req(t, "parameter").contiguous()
+        P4 = k4.shape[1] if k4 is not None and k4.dim() == 2 else 1
+        P4i = k4i.shape[1] if k4i is not None and k4i.dim() == 2 else 1
+        k2, eq2 = prep(k2, (T["n2"],)), prep(eq2, (T["n2"],))
+        k3, eq3 = prep(k3, (T["n3"],)), prep(eq3, (T["n3"],))
+        k4, k4i = prep(k4, (T["n4"], P4)), prep(k4i, (T["n4_improper"], P4i))
+        es = plan.energy_sizes
+        n_mol = plan.n_mol
+        energy = torch.empty((n_mol, C), device=dev, dtype=torch.float32)
+        term = torch.empty((4, n_mol, C), device=dev, dtype=torch.float32)
+        grad = torch.empty((N, C, 3), device=dev, dtype=torch.float32)
+        lv = ("n2", "n3", "n4", "n4_improper")
+        xs = [torch.empty((T[l], C), device=dev, dtype=torch.float32) if want_coords else None for l in lv]
+        ts = [torch.empty((T[l], C), device=dev, dtype=torch.float32) if want_coords else None for l in lv]
+        partial = torch.empty((es["n_blocks"], 4, C), device=dev, dtype=torch.float32) if es["any_multi"] else None
+        _lib.check(_lib.lib().grappa_energy_fwd(
+            N, n_mol, C, _p(xyz), es["n_blocks"], plan.ptr("e_blk"), plan.ptr("e_rec_atoms"), plan.ptr("e_rec_meta"),
+            plan.ptr("e_rec_slot"), plan.ptr("e_pull_ptr"), plan.ptr("e_pull_slot"), es["max_slots"], es["any_multi"], term_mask,
+            _p(k2), _p(eq2), _p(k3), _p(eq3), _p(k4), P4, _p(k4i), P4i, _p(energy), _p(term), _p(grad),
+            _p(xs[0]), _p(xs[1]), _p(xs[2]), _p(xs[3]), _p(ts[0]), _p(ts[1]), _p(ts[2]), _p(ts[3]), _p(partial), _stream()))
+        ctx.save_for_backward(xyz, k2, eq2, k3, eq3, k4, k4i)
+        ctx.cfg = (plan, P4, P4i, term_mask)
+        outs = [energy, grad, term] + [x if x is not None else torch.empty(0, device=dev) for x in xs] + \
+               [t if t is not None else torch.empty(0, device=dev) for t in ts]
+        ctx.mark_non_differentiable(*outs[2:])
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, g_energy, g_grad, *unused):
+        xyz, k2, eq2, k3, eq3, k4, k4i = ctx.saved_tensors
+        plan, P4, P4i, term_mask = ctx.cfg
+        if term_mask != 15:
+            raise NotImplementedError("backward through a term-masked Energy evaluation is not supported")
+        T = plan.T
+        dev = xyz.device
+        C = xyz.shape[1]
+        g_energy = g_energy.contiguous() if g_energy is not None else None
+        g_grad = g_grad.contiguous() if g_grad is not None else None
+        dk2, deq2 = torch.empty_like(k2), torch.empty_like(eq2)
+        dk3, deq3 = torch.empty_like(k3), torch.empty_like(eq3)
+        dk4, dk4i = torch.empty_like(k4), torch.empty_like(k4i)
+        s, n = plan.offsets["tuple_mol"]
+        _lib.check(_lib.lib().grappa_energy_vjp(
+            C, _p(xyz), _p(g_energy), _p(g_grad), plan.ptr("tuple_mol"),
+            plan.ptr("idx_n2"), T["n2"], plan.ptr("idx_n3"), T["n3"], plan.ptr("idx_n4"), T["n4"],
+            plan.ptr("idx_n4_improper"), T["n4_improper"],
+            _p(k2), _p(eq2), _p(k3), _p(eq3), _p(k4), P4, _p(k4i), P4i,
+            _p(dk2), _p(deq2), _p(dk3), _p(deq3), _p(dk4), _p(dk4i), _stream()))
+        ng = ctx.needs_input_grad
+        return (dk2 if ng[0] else None, deq2 if ng[1] else None, dk3 if ng[2] else None, deq3 if ng[3] else None,
+                dk4 if ng[4] else None, dk4i if ng[5] else None, None, None, None, None)
+
+
+class MolwiseLossFn(torch.autograd.Function):
+    """Fused molecule-wise loss; the backward re-runs the kernel with gradient outputs scaled by the upstream scalar."""
+
+    @staticmethod
+    def _call(plan, weights, energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy, upstream, parts, loss, dE, dG, dk4, dk4i):
+        ew, gw, preg, ireg = weights
+        n_mol, C = energy.shape
+        _lib.check(_lib.lib().grappa_molwise_loss(
+            n_mol, C, plan.ptr("mol_atom_off"), plan.ptr("mol_off_n4"), plan.ptr("mol_off_n4_improper"),
+            _p(energy), _p(energy_ref), _p(gradient), _p(gradient_ref), _p(is_dummy),
+            _p(k4), k4.shape[1] if k4.dim() == 2 else 1, _p(k4i), k4i.shape[1] if k4i.dim() == 2 else 1,
+            ew, gw, preg, ireg, _p(upstream), _p(parts), _p(loss), _p(dE), _p(dG), _p(dk4), _p(dk4i), _stream()))
+
+    @staticmethod
+    def forward(ctx, energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy, plan, weights):
+        energy = _req(energy, "energy").contiguous()
+        gradient = _req(gradient, "gradient").contiguous()
+        k4, k4i = k4.contiguous(), k4i.contiguous()
+        energy_ref, gradient_ref = energy_ref.contiguous(), gradient_ref.contiguous()
+        is_dummy = is_dummy.contiguous() if is_dummy is not None else None
+        dev = energy.device
+        parts = torch.empty((energy.shape[0],), device=dev, dtype=torch.float32)
+        loss = torch.empty((), device=dev, dtype=torch.float32)
+        MolwiseLossFn._call(plan, weights, energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy, None, parts, loss,
+                            None, None, None, None)
+        ctx.save_for_backward(energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy)
+        ctx.cfg = (plan, weights)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy = ctx.saved_tensors
+        plan, weights = ctx.cfg
+        g = g.contiguous().float()
+        dE, dG = torch.empty_like(energy), torch.empty_like(gradient)
+        dk4, dk4i = torch.empty_like(k4), torch.empty_like(k4i)
+        MolwiseLossFn._call(plan, weights, energy, gradient, k4, k4i, energy_ref, gradient_ref, is_dummy, g, None, None,
+                            dE, dG, dk4, dk4i)
+        return dE, dG, dk4, dk4i, None, None, None, None, None

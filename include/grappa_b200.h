@@ -1,0 +1,209 @@
+/*
+ * grappa_b200 — C ABI of the B200-native Grappa hot path (libgrappa_b200.so).
+ *
+ * The reference (graeter-group/grappa) is pure Python: its "FFI" for this path is the set of PyTorch / DGL library
+ * calls made by src/grappa/models/*.py.  Every entry point below replaces one such call site (cited per function,
+ * paths relative to the reference root).  The Python wrappers in grappa_b200/ bind these with ctypes; they are
+ * the only callers.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  Unless a parameter is marked HOST it is a device pointer.
+ *   - all floating point is fp32, indices are int32 on the device (the graph's int64 idxs are narrowed once by the
+ *     host plan), row-major, leading dimensions in elements.
+ *   - `stream` is a cudaStream_t passed as void*.  Calls are asynchronous on that stream and hold no global state.
+ *   - return value 0 = success; otherwise grappa_last_error() (thread-local) describes the failure.
+ *   - nothing here allocates device memory: outputs and scratch are caller-provided.
+ */
+#ifndef GRAPPA_B200_H
+#define GRAPPA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* grappa_last_error(void);
+int grappa_abi_version(void);
+/* number of kernel launches issued through this library by the calling process (for bench.py's gpu_launches) */
+int64_t grappa_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Dense layers.  Replaces torch.nn.Linear / F.linear + ELU + Dropout + residual adds at
+ *   models/graph_attention.py:179,300-307,315-321,190  models/interaction_parameters.py:172
+ *   models/network_utils.py:47-53,123-134  models/perm_equiv_transformer.py:282
+ * C[M,N] = dropout(act(A·op(B) + bias)) + res1 + res2
+ *   layout 0 ("NT"): A is (M,K) row-major, B is (N,K) row-major (a torch Linear weight)      -> forward
+ *   layout 1 ("NN"): A is (M,K) row-major, B is (K,N) row-major                               -> dX = dZ·W
+ *   layout 2 ("TN"): A is (K,M) row-major (used transposed), B is (K,N) row-major             -> dW = dZ^T·X
+ * act: 0 none, 1 ELU(alpha=1).  bias (N) / res1 / res2 may be NULL.  drop_p in [0,1): keep-mask from a
+ * counter-based hash of (seed + *seed_dev, row*N+col), kept values scaled by 1/(1-p).  seed_dev (device, may be
+ * NULL) lets a captured CUDA graph draw fresh masks on every replay: the step driver bumps it between steps.
+ * math_mode: 0 = fp32 FFMA tiles, 1 = tcgen05 3xTF32 (split-precision tensor-core tiles, fp32-level accuracy).
+ */
+int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
+                const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode, void* stream);
+
+/* dZ = dY * keepmask/(1-p) * act'(.) where the activation output is recovered as (Y - res1 - res2)*(1-p).
+ * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL. */
+int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,
+                        const float* res1, int64_t ldr1, const float* res2, int64_t ldr2, int act,
+                        float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz, void* stream);
+
+/* out[n] = sum_m X[m,n]  (bias gradients).  scratch: at least grappa_colsum_scratch_floats(M,N) floats. */
+int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N);
+int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch, void* stream);
+
+/* LayerNorm over the last dimension (eps 1e-5).  Replaces torch.nn.LayerNorm at graph_attention.py:293,312,
+ * network_utils.py:46,115,129, perm_equiv_transformer.py:80.  mean/rstd: (M) saved for backward. */
+int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_t ldx, const float* gamma, const float* beta,
+                         float* Y, int64_t ldy, float* mean, float* rstd, void* stream);
+int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D);
+int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64_t lddy, const float* X, int64_t ldx,
+                         const float* gamma, const float* mean, const float* rstd,
+                         float* dX, int64_t lddx, float* dgamma, float* dbeta, float* scratch, void* stream);
+
+/* Atom featurisation.  Replaces the torch.cat / one_hot chain at graph_attention.py:156-177,446-464.
+ * blocks: up to 8 (ptr, width, ld) feature blocks concatenated in order, followed by the 16-wide charge encoding
+ * of `charge` (n_atoms) [normalised value, one-hot over 15 bins of [-2,2]].  A NULL block pointer writes zeros. */
+int grappa_featurize(int64_t n_atoms, int n_blocks, const float* const* block_ptr /*HOST array*/,
+                     const int32_t* block_width /*HOST*/, const int32_t* block_ld /*HOST*/,
+                     const float* charge, float* out, int64_t ldo, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Graph attention message passing.  Replaces dgl.nn.pytorch.conv.DotGatConv.forward after its `fc` Linear
+ * (graph_attention.py:262,296; DGL 2.4.0 dotgatconv.py: u_dot_v / sqrt(D), edge_softmax by destination, u_mul_e sum).
+ * ft: (N, H*D).  in_ptr (N+1) / in_src: CSR of incoming edges by destination; out_ptr / out_dst: CSR of outgoing
+ * edges by source.  lse: (N,H) log-sum-exp saved for backward.  H*D must be a multiple of 128 and D one of 16,32,64.
+ */
+int grappa_gnn_attn_fwd(int64_t N, int H, int D, const float* ft, const int32_t* in_ptr, const int32_t* in_src,
+                        float* out, float* lse, void* stream);
+int grappa_gnn_attn_bwd(int64_t N, int H, int D, const float* ft, const float* out, const float* lse,
+                        const float* dOut, const int32_t* in_ptr, const int32_t* in_src,
+                        const int32_t* out_ptr, const int32_t* out_dst,
+                        float* delta /*scratch (N,H)*/, float* dft, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Interaction readout.
+ * tuple_gather: X[t, i, 0:F] = A[idx[t,i], 0:F]; X[t, i, F:W] = pe[i]  -> tokens (T*n_seq, W), tuple-major.
+ * Replaces RepProjector's advanced-index gather + transpose (interaction_parameters.py:184-189) and the
+ * positional-encoding concat (perm_equiv_transformer.py:152-159).  Backward is a pull reduction over the
+ * atom -> token incidence CSR (inc_ptr (N+1), inc_tok), no atomics. */
+int grappa_tuple_gather_fwd(int64_t T, int n_seq, int F, int W, const float* A, int64_t lda, const int32_t* idx,
+                            const float* pe /*(n_seq) or NULL*/, float* X, void* stream);
+int grappa_tuple_gather_bwd(int64_t N, int F, int W, const float* dX, const int32_t* inc_ptr, const int32_t* inc_tok,
+                            float* dA, int64_t ldda, void* stream);
+
+/* Self-attention over the n_seq <= 4 tokens of every tuple (nn.MultiheadAttention core, network_utils.py:123).
+ * qkv: (T*n_seq, 3*E) = [q | k | v], E = n_heads*head_dim, head_dim 64.  out: (T*n_seq, E). */
+int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, float* out, void* stream);
+int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const float* dOut,
+                          float* dqkv, void* stream);
+
+/* R = X3 + X * (col < F ? 2 : 1): the two input residuals around the transformer
+ * (perm_equiv_transformer.py:165 and :75-77).  Backward: dX = dR * (col < F ? 2 : 1). */
+int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, float* R, void* stream);
+int grappa_token_residual_bwd(int64_t M, int W, int F, const float* dR, float* dX, void* stream);
+
+/* Symmetriser input: rows (P*T, n_seq*W) with row p*T+t = concat_i X[t, perm[p][i], :]
+ * (perm_equiv_transformer.py:266-279).  perm: HOST (P*n_seq) ints.  Backward sums the permuted views back. */
+int grappa_symm_permute_fwd(int64_t T, int n_seq, int W, int P, const int32_t* perm /*HOST*/, const float* X,
+                            float* Y, void* stream);
+int grappa_symm_permute_bwd(int64_t T, int n_seq, int W, int P, const int32_t* perm /*HOST*/, const float* dY,
+                            float* dX, void* stream);
+
+/* Sum over permutations (perm_equiv_transformer.py:288-292) fused with the range maps
+ * (final_layer.py:48-52, 91-97; interaction_parameters.py:276-288, 382-395, 586-611; network_utils.py:147-148).
+ * S: (P*T, n_out) symmetriser outputs; prefactor: HOST (P).
+ * kind 0 bond : eq = to_positive(c0; eq_mos, eq_std, eq_min)   k = to_positive(c1; k_mos, k_std, k_min)
+ * kind 1 angle: eq = eq_max * sigmoid(eq_som * c0)             k = to_positive(c1; ...)
+ * kind 2 torsion (gated): k[:, col0 + j] = cutoff( c[j] * sigmoid(c[n_half + j]) * k_std[j] ), other columns 0.
+ * kind 3 torsion (ungated): k[:, col0 + j] = cutoff( c[j] * k_std[j] + k_mean[j] ).
+ * consts: HOST float[8] = {eq_a, eq_b, eq_c, k_mos, k_std, k_min, cutoff, unused}; bond: eq_a=mean_over_std,
+ * eq_b=std, eq_c=min; angle: eq_a=std_over_max, eq_b=max.  kstd / kmean: device (n_half) for kinds 2, 3.
+ * C: (T, n_out) pre-map sums saved for backward. */
+int grappa_readout_finalize_fwd(int kind, int64_t T, int P, int n_out, const float* S, const float* prefactor,
+                                const float* consts, const float* kstd, const float* kmean, int n_per, int col0,
+                                float* C, float* eq, float* k, void* stream);
+int grappa_readout_finalize_bwd(int kind, int64_t T, int P, int n_out, const float* C, const float* prefactor,
+                                const float* consts, const float* kstd, const float* kmean, int n_per, int col0,
+                                const float* d_eq, const float* d_k, float* dS, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * MM energy + analytic dE/dxyz.  Replaces internal_coordinates (internal_coordinates.py:19-115),
+ * harmonic_energy / torsion_energy / pool_energy (energy.py:8-71) and the autograd.grad call (energy.py:160-164).
+ *
+ * The host plan partitions the atoms of every molecule into blocks of <= block_atoms consecutive atoms and lists,
+ * per block, every tuple touching it (tuples spanning blocks are evaluated once per block they touch; only the
+ * owner block adds their energy).  grappa_energy_plan_build fills caller-provided HOST int32 arrays; call it first
+ * with all output pointers NULL to obtain the sizes in sizes_out[8] =
+ *   {n_blocks, n_records, n_pull, max_slots_per_block, max_records_per_block, max_atoms_per_block, any_multi_block, 0}.
+ * idx2/3/4/4i: HOST int64 (T,n_seq) global atom rows; mol_atom_off: HOST int64 (n_mol+1).
+ */
+int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
+                             const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
+                             const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
+                             int block_atoms, int64_t* sizes_out,
+                             int32_t* blk /*(n_blocks,8)*/, int32_t* rec_atoms /*(n_records,4)*/,
+                             int32_t* rec_meta /*(n_records,2)*/, int32_t* rec_slot /*(n_records,4)*/,
+                             int32_t* pull_ptr /*(n_atoms+1)*/, int32_t* pull_slot /*(n_pull)*/,
+                             int32_t* tuple_mol /*(T2+T3+T4+T4i)*/);
+
+/* All plan arrays are the device copies of the arrays above.  k4: (T4,P4), k4i: (T4i,P4i).
+ * Outputs: energy (n_mol,C) total; term_energy (4,n_mol,C); gradient (N,C,3) = +dE/dxyz.
+ * Optional (may be NULL): x2,x3,x4,x4i (T,C) internal coordinates; e2,e3,e4,e4i (T,C) per-tuple energies.
+ * partial: scratch (n_blocks,4,C) floats, used only when a molecule spans several blocks.
+ * term_mask: bit l set = include level l (0 bond, 1 angle, 2 proper, 3 improper); 15 = all.  Sub-masks give the
+ * per-term gradients of Energy(gradient_contributions=True) (energy.py:146-152). */
+int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, const float* xyz,
+                      int64_t n_blocks, const int32_t* blk, const int32_t* rec_atoms, const int32_t* rec_meta,
+                      const int32_t* rec_slot, const int32_t* pull_ptr, const int32_t* pull_slot,
+                      int max_slots, int any_multi_block, int term_mask,
+                      const float* k2, const float* eq2, const float* k3, const float* eq3,
+                      const float* k4, int P4, const float* k4i, int P4i,
+                      float* energy, float* term_energy, float* gradient,
+                      float* x2, float* x3, float* x4, float* x4i, float* e2, float* e3, float* e4, float* e4i,
+                      float* partial, void* stream);
+
+/* Vector-Jacobian product of (energy, gradient) w.r.t. the MM parameters for the training loss
+ * (double backward through energy.py:162 in closed form, SURVEY.md §7 "Double backward").
+ * gE: (n_mol,C) dL/d energy (may be NULL), gG: (N,C,3) dL/d gradient (may be NULL).
+ * idx*: device int32 (T,n_seq); tuple_mol: device int32 (T2+T3+T4+T4i), molecule of each tuple. */
+int grappa_energy_vjp(int64_t C, const float* xyz, const float* gE, const float* gG, const int32_t* tuple_mol,
+                      const int32_t* idx2, int64_t T2, const int32_t* idx3, int64_t T3,
+                      const int32_t* idx4, int64_t T4, const int32_t* idx4i, int64_t T4i,
+                      const float* k2, const float* eq2, const float* k3, const float* eq3,
+                      const float* k4, int P4, const float* k4i, int P4i,
+                      float* dk2, float* deq2, float* dk3, float* deq3, float* dk4, float* dk4i, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------
+ * Host helpers (HOST pointers only).
+ * Stable counting sort of n items by key in [0,n_keys): ptr (n_keys+1), order (n) = item ids grouped by key in
+ * their original order.  Used for CSR-by-destination / by-source of the bond edges and the atom -> token incidence. */
+int grappa_csr_build(int64_t n, int64_t n_keys, const int64_t* keys, int32_t* ptr, int32_t* order);
+
+/* Training-side fused kernels (next rows of SURVEY.md §8f, used by the data-parallel step driver). */
+/* Molecule-wise loss (training/loss.py:51-174 with param_weight 0): forward value and gradients w.r.t. energy,
+ * gradient and the torsion force constants in one pass.  loss_parts: (n_mol) per-molecule terms (already / n_mol);
+ * the scalar loss is their sum in molecule order (written to loss_out). */
+int grappa_molwise_loss(int64_t n_mol, int64_t C, const int32_t* mol_atom_off, const int32_t* mol_p_off,
+                        const int32_t* mol_i_off, const float* energy, const float* energy_ref,
+                        const float* gradient, const float* gradient_ref, const float* is_dummy,
+                        const float* k4, int P4, const float* k4i, int P4i,
+                        float energy_weight, float gradient_weight, float proper_reg, float improper_reg,
+                        const float* upstream /*device scalar or NULL: scales dE,dG,dk4,dk4i*/,
+                        float* loss_parts, float* loss_out, float* dE, float* dG, float* dk4, float* dk4i,
+                        void* stream);
+
+/* AdamW over one flat parameter buffer (torch.optim.AdamW semantics, lightning_model.py:368-370).
+ * grad_scale multiplies the gradient first (1/world_size after an allreduce-sum). */
+int grappa_adamw(int64_t n, float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                 float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                 void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAPPA_B200_H */
