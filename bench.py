@@ -1,0 +1,349 @@
+#!/usr/bin/env python
+"""
+bench.py — headline benchmark of the Grappa hot path on B200 (contract: see the task statement / DESIGN.md §Measurement).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (one process per GPU under torchrun for N > 1)
+  python bench.py --impl reference [--steps K] [--warmup W]       the reference's algorithm on the host cores (oracle port)
+
+Workload at N = 1: BASELINE.json configs[1] — one training step (GrappaModel -> Energy -> molecule-wise loss ->
+backward -> AdamW, dropout active) on a synthetic SPICE-like batch of 32 molecules x 40 atoms x 50 conformations.
+For N > 1 every rank owns its own 32-molecule slice (weak scaling) and gradients are all-reduced over NCCL.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch  # noqa: E402
+
+MOLS_PER_RANK = 32
+N_CONFS = 50
+WORKLOAD = ("cfg2: training step (fwd + molecule-wise energy/force loss + bwd + AdamW, dropout on), "
+            "32 molecules x 40 atoms x 50 conformations per GPU, default Grappa model (20.8 M params)")
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            d = json.load(f)
+        return d, "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def __enter__(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_batch(first_seed: int, n_mol: int = MOLS_PER_RANK, n_confs: int = N_CONFS):
+    from grappa_b200 import synthetic as S
+    return S.cfg2_batch(n_mol, n_confs, first_seed)
+
+
+def cpu_train_baseline(sd, g, steps: int, warmup: int, budget_s: float = 25.0):
+    """Oracle training step (dropout on, AdamW) on all host threads; bounded sample of the same workload."""
+    import grappa_oracle as O
+    from grappa_b200.graph import batch, unbatch
+    torch.set_num_threads(os.cpu_count() or 1)
+    torch.set_float32_matmul_precision("highest")
+    tr = O.OracleTrainer(sd)
+    n_mol = g.batch_size
+    t0 = time.perf_counter()
+    tr.step(g)
+    t_first = time.perf_counter() - t0
+    sample_mols = n_mol
+    if t_first * (steps + max(warmup - 1, 0)) > budget_s and n_mol > 8:
+        sample_mols = 8
+        parts = unbatch(g)[:8]
+        # unbatch() returns views with local idxs; re-batch the first 8 molecules
+        g = batch(parts)
+    for _ in range(max(warmup - 1, 0)):
+        tr.step(g)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        tr.step(g)
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": sample_mols / dt, "unit": "molecules/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{steps} training steps (+{warmup} warm-up) of {sample_mols} molecules x 40 atoms x {N_CONFS} conformations, "
+                      f"oracle port of the reference (PyTorch CPU fp32, dropout on, AdamW), {dt * 1e3:.0f} ms/step"}, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's algorithm (oracle port; /root/reference cannot travel and needs DGL) on host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from grappa_b200.model import GrappaModel
+    torch.manual_seed(0)
+    sd = GrappaModel.from_default_config().state_dict()
+    g = build_batch(0)
+    steps = max(1, min(args.steps, 10))
+    base, dt = cpu_train_baseline(sd, g, steps=steps, warmup=max(1, min(args.warmup, 2)), budget_s=150.0)
+    line = {"impl": "reference", "metric": "train_molecules_per_s", "value": base["value"], "unit": "molecules/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": max(1, min(args.warmup, 2)), "ms_per_step": dt * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": MOLS_PER_RANK, "note": "CPU oracle port; runs on rank 0 only"},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the inference / energy-sweep side measurements")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
+    ap.add_argument("--math-mode", type=int, default=None)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    from grappa_b200 import _lib, ops
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.model import GrappaModel
+    from grappa_b200.train_step import TrainStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+    if args.math_mode is not None:
+        ops.MATH_MODE = args.math_mode
+    K, W = args.steps, max(args.warmup, 3)
+
+    torch.manual_seed(0)                       # identical random-init weights on every rank
+    model = GrappaModel.from_default_config()
+    sd_cpu = {k: v.clone() for k, v in model.state_dict().items()}
+    ts = TrainStep(model, dev, lr=1e-5, weight_decay=0.0, world_size=world, use_cuda_graph=not args.no_graph)
+    ops.DropoutSeeds.manual_seed(1234 + rank)  # dropout streams differ per rank
+    g_host = build_batch(first_seed=MOLS_PER_RANK * rank)
+    packed = PackedBatch(g_host, pin=True)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up (includes CUDA-graph capture after two eager steps) ----
+    l0 = _lib.launch_count()
+    ts.step(packed, load=True)
+    torch.cuda.synchronize()
+    launches_per_step = _lib.launch_count() - l0
+    for _ in range(max(W - 1, 3)):
+        ts.step(packed, load=True)
+    barrier()
+
+    # ---- timed region 1: device-resident inputs ----
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        start.record()
+        for _ in range(K):
+            loss = ts.step(packed, load=False)
+        end.record()
+        barrier()
+    ms = start.elapsed_time(end)
+    # ---- timed region 2: end to end (pinned host -> device copies and loss read-back inside) ----
+    barrier()
+    start2, end2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start2.record()
+    last = 0.0
+    for _ in range(K):
+        last = ts.step(packed, load=True).item()
+    end2.record()
+    barrier()
+    ms2 = start2.elapsed_time(end2)
+    t = torch.tensor([ms, ms2], device=dev, dtype=torch.float64)
+    if world > 1:
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    ms, ms2 = float(t[0]), float(t[1])
+    mols = MOLS_PER_RANK * world
+
+    line = {"metric": "train_molecules_per_s", "value": mols * K / (ms * 1e-3), "unit": "molecules/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": mols, "parallelism": f"dp{world}",
+                       "gemm_math": "fp32 FFMA" if ops.MATH_MODE == 0 else "tcgen05 3xTF32",
+                       "cuda_graph": not args.no_graph,
+                       "l2": "no explicit flush: one step touches parameters + gradients + Adam state (4 x 83 MB) plus "
+                             "~0.5 GB of activations, several times the 126 MB L2"},
+            "e2e": {"value": mols * K / (ms2 * 1e-3), "unit": "molecules/s", "h2d_bytes_per_step": packed.h2d_bytes,
+                    "d2h_bytes_per_step": 4, "ms_per_step": ms2 / K},
+            "gpu_launches": int(launches_per_step * K), "final_loss": last}
+    if rank == 0:
+        line["clocks"] = clocks.summary()
+
+    # ---- per-kernel timing with CUDA events (eager pass, rank 0) -> roofline ----
+    if rank == 0:
+        pk, pk_src = peaks()
+        _lib.PROFILE_HINTS.update(n_edges=g_host.num_edges(), n_atoms=g_host.num_nodes("n1"))
+        ts_graph = ts.use_cuda_graph
+        ts.use_cuda_graph = False
+        for _ in range(2):
+            ts.compute_gradients(packed, load=False)
+        _lib.profiler = _lib.Profiler()
+        n_prof = 3
+        for _ in range(n_prof):
+            ts.compute_gradients(packed, load=False)
+            ts.optimizer_step()
+        summ = _lib.profiler.summary()
+        _lib.profiler = None
+        ts.use_cuda_graph = ts_graph
+        tot = sum(d["ms"] for d in summ.values())
+        kern = {k: {"ms_per_step": d["ms"] / n_prof, "share": d["ms"] / tot, "calls_per_step": d["calls"] / n_prof} for k, d in summ.items()}
+        gm = summ["grappa_gemm"]
+        tf = gm["flops"] / (gm["ms"] * 1e-3) / 1e12
+        peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+        line["roofline"] = {"kernel": "sgemm_kernel (grappa_gemm, all layouts, fused bias/ELU/dropout/residual epilogue)",
+                            "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                            "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
+                            "pipe": "fp32 FFMA (math_mode 0)" if ops.MATH_MODE == 0 else "tcgen05 kind::tf32 x3",
+                            "share_of_step": gm["ms"] / tot,
+                            "flops_per_step": gm["flops"] / n_prof, "ms_per_step": gm["ms"] / n_prof}
+        others = {}
+        for name, label in (("grappa_energy_fwd", "energy_fwd"), ("grappa_energy_vjp", "energy_vjp"), ("grappa_gnn_attn_fwd", "gnn_attn_fwd")):
+            if name in summ and summ[name]["ms"] > 0:
+                d = summ[name]
+                gbs = d["bytes"] / (d["ms"] * 1e-3) / 1e9
+                others[label] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                                 "ms_per_call": d["ms"] / d["calls"]}
+        line["roofline_other_kernels"] = others
+        line["kernel_time_shares"] = {k: round(v["share"], 4) for k, v in sorted(kern.items(), key=lambda kv: -kv[1]["share"])}
+
+    # ---- side measurements on rank 0: inference (cfg 3) and energy sweep (cfg 4) ----
+    if rank == 0 and world == 1 and not args.no_extras:
+        line["extra"] = extras(dev, pk)
+    if world > 1:
+        torch.distributed.barrier()
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        base, _ = cpu_train_baseline(sd_cpu, g_host, steps=3, warmup=1)
+        line["cpu_baseline"] = base
+    elif rank == 0:
+        line["cpu_baseline"] = None
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+def extras(dev, pk):
+    """BASELINE.json configs[2] (inference atoms/s, 15k-atom system) and configs[3] (energy sweep, 1000 x 500)."""
+    from grappa_b200 import synthetic as S
+    from grappa_b200.energy import Energy
+    from grappa_b200.model import GrappaModel
+    out = {}
+    torch.manual_seed(0)
+    model = GrappaModel.from_default_config().to(dev).eval()
+    g = S.cfg3_graph().to(dev)
+    with torch.no_grad():
+        for _ in range(3):
+            model(g)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 10
+        a.record()
+        for _ in range(n):
+            model(g)
+        b.record()
+        torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / n
+    out["inference_cfg3"] = {"atoms": g.num_nodes("n1"), "ms": ms, "atoms_per_s": g.num_nodes("n1") / (ms * 1e-3),
+                             "algorithmic_tflop": 1.7, "tflops": 1.7 / (ms * 1e-3)}
+    del g
+    g4 = S.cfg4_batch(1000, 500).to(dev)
+    k_src = S.trimer_molecule(0, 1).to(dev)
+    with torch.no_grad():
+        k_src = model(k_src)
+    for lvl in ("n2", "n3", "n4", "n4_improper"):
+        for key in ("k", "eq"):
+            if key in k_src.nodes[lvl].data:
+                v = k_src.nodes[lvl].data[key]
+                g4.nodes[lvl].data[key] = v.repeat(1000, *([1] * (v.dim() - 1))).contiguous()
+    en = Energy(materialize_tuple_terms=False)
+    with torch.no_grad():
+        for _ in range(3):
+            en(g4)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 10
+        a.record()
+        for _ in range(n):
+            en(g4)
+        b.record()
+        torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / n
+    units = 1000 * 500
+    gbs = units * (24 * 40 + 20) / (ms * 1e-3) / 1e9
+    out["energy_cfg4"] = {"mol_conf_per_s": units / (ms * 1e-3), "ms": ms, "algorithmic_GBps": gbs, "hbm_frac": gbs / pk["hbm_gbs"]}
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -56,7 +56,66 @@ class GrappaKernelError(RuntimeError):
     pass
 
 
+class Profiler:
+    """Per-entry-point CUDA-event timing on the launching stream (used by bench.py for the roofline numbers).
+    Enabled with `_lib.profiler = Profiler()`; every C-ABI call is then bracketed by two events."""
+
+    def __init__(self):
+        self.records = []          # (name, start_event, end_event, args)
+
+    def summary(self):
+        import torch
+        torch.cuda.synchronize()
+        out = {}
+        for name, a, b, args in self.records:
+            d = out.setdefault(name, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            d["calls"] += 1
+            d["ms"] += a.elapsed_time(b)
+            if name == "grappa_gemm":
+                d["flops"] += 2.0 * args[1] * args[2] * args[3]
+            elif name == "grappa_energy_fwd":                      # 24 B per atom-conformation + 20 B per molecule-conformation
+                d["bytes"] += args[2] * (24.0 * args[0] + 20.0 * args[1])
+            elif name == "grappa_energy_vjp":
+                d["bytes"] += args[0] * 24.0 * PROFILE_HINTS.get("n_atoms", 0)
+            elif name == "grappa_gnn_attn_fwd":                    # (2N + E) rows of H*D floats
+                d["bytes"] += (2.0 * args[0] + PROFILE_HINTS.get("n_edges", 0)) * args[1] * args[2] * 4.0
+        return out
+
+
+PROFILE_HINTS = {}
+profiler = None
+
+
+class _ProfiledLib:
+    def __init__(self, handle, prof):
+        self._h, self._p = handle, prof
+
+    def __getattr__(self, name):
+        fn = getattr(self._h, name)
+        if not name.startswith("grappa_") or name in ("grappa_last_error", "grappa_launch_count", "grappa_abi_version",
+                                                       "grappa_colsum_scratch_floats", "grappa_layernorm_bwd_scratch_floats",
+                                                       "grappa_csr_build", "grappa_energy_plan_build"):
+            return fn
+        prof = self._p
+
+        def timed(*args):
+            import torch
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            rc = fn(*args)
+            b.record()
+            prof.records.append((name, a, b, args))
+            return rc
+        return timed
+
+
 def lib():
+    if profiler is not None:
+        return _ProfiledLib(_raw_lib(), profiler)
+    return _raw_lib()
+
+
+def _raw_lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
@@ -79,4 +138,4 @@ def check(rc: int):
 
 
 def launch_count() -> int:
-    return int(lib().grappa_launch_count())
+    return int(_raw_lib().grappa_launch_count())

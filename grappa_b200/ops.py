@@ -13,6 +13,10 @@ from . import _lib
 
 MATH_MODE = 0          # 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm)
 ACT_NONE, ACT_ELU = 0, 1
+# Optional {id(parameter): gradient buffer}: backward kernels write parameter gradients straight into these buffers
+# (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
+# Valid because every parameter of the model is used exactly once per forward.
+GRAD_SINK = None
 
 
 def _stream():
@@ -91,6 +95,7 @@ class LinearFn(torch.autograd.Function):
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
                               r2 if act != ACT_NONE else None)
         ctx.cfg = (act, float(drop_p), seed, seed_dev, N, ldc, bias is not None, res1 is not None, res2 is not None)
+        ctx.sink_ids = (id(weight), id(bias))
         return y
 
     @staticmethod
@@ -113,13 +118,20 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
             gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
+        sink = GRAD_SINK
         if ctx.needs_input_grad[1]:
-            dw = torch.empty((N, K), device=dy.device, dtype=torch.float32)
+            tgt = sink.get(ctx.sink_ids[0]) if sink is not None else None
+            dw = tgt if tgt is not None else torch.empty((N, K), device=dy.device, dtype=torch.float32)
             gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
+            if tgt is not None:
+                dw = None
         if has_bias and ctx.needs_input_grad[2]:
-            db = torch.empty((N,), device=dy.device, dtype=torch.float32)
+            tgt = sink.get(ctx.sink_ids[1]) if sink is not None else None
+            db = tgt if tgt is not None else torch.empty((N,), device=dy.device, dtype=torch.float32)
             scratch = torch.empty((int(L.grappa_colsum_scratch_floats(M, N)),), device=dy.device, dtype=torch.float32)
             _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
+            if tgt is not None:
+                db = None
         dr = dy if ldc == N else dy[:, :N]
         return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,
                 dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None)
@@ -139,6 +151,7 @@ class LayerNormFn(torch.autograd.Function):
         _lib.check(_lib.lib().grappa_layernorm_fwd(M, D, _p(x), ldx, _p(gamma), _p(beta), _p(y), D, _p(stats[0]), _p(stats[1]),
                                                    _stream()))
         ctx.save_for_backward(x, gamma, stats)
+        ctx.sink_ids = (id(gamma), id(beta))
         return y
 
     @staticmethod
@@ -151,12 +164,19 @@ class LayerNormFn(torch.autograd.Function):
         dx = torch.empty((M, D), device=dy.device, dtype=torch.float32)
         need_affine = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
         dg = db = scratch = None
+        sunk = False
         if need_affine:
-            dg = torch.empty((D,), device=dy.device, dtype=torch.float32)
-            db = torch.empty((D,), device=dy.device, dtype=torch.float32)
+            sink = GRAD_SINK
+            tg = sink.get(ctx.sink_ids[0]) if sink is not None else None
+            tb = sink.get(ctx.sink_ids[1]) if sink is not None else None
+            sunk = tg is not None and tb is not None
+            dg = tg if sunk else torch.empty((D,), device=dy.device, dtype=torch.float32)
+            db = tb if sunk else torch.empty((D,), device=dy.device, dtype=torch.float32)
             scratch = torch.empty((int(L.grappa_layernorm_bwd_scratch_floats(M, D)),), device=dy.device, dtype=torch.float32)
         _lib.check(L.grappa_layernorm_bwd(M, D, _p(dy), lddy, _p(x), ldx, _p(gamma), _p(stats[0]), _p(stats[1]), _p(dx), D,
                                           _p(dg), _p(db), _p(scratch), _stream()))
+        if sunk:
+            dg = db = None
         return dx, dg, db
 
 

@@ -1,0 +1,140 @@
+"""
+Data-parallel training-step driver.  Replaces, for benchmarking and as the minimal trainer, the
+Lightning orchestration of training/lightning_model.py:228-254,368-370: forward (GrappaModel -> Energy), molecule-wise
+loss, backward, gradient all-reduce over NCCL (one process per GPU), AdamW.
+
+B200-first design choices
+  - parameters live in ONE flat fp32 buffer and their gradients in another: the backward GEMMs write weight
+    gradients straight into the flat gradient buffer (ops.GRAD_SINK), the all-reduce is a single NCCL call over
+    83 MB, AdamW is a single kernel launch;
+  - inputs arrive as two pinned host buffers (batching.PackedBatch) copied into static device buffers;
+  - forward + loss + backward are captured once per batch shape in a CUDA graph and replayed; dropout masks stay
+    fresh across replays through a device-side seed that the graph itself increments.
+Molecules are independent units: rank r owns a contiguous slice of the global batch, no data-path collective exists
+other than the gradient all-reduce.
+"""
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib, ops
+from .batching import DeviceBatch, PackedBatch
+from .energy import Energy
+from .plan import get_plan
+
+# parameters that the reference registers but never uses (perm_equiv_transformer.py:126): no gradient, not optimised
+_UNUSED = ("grappa_transformer.norm.",)
+
+
+class FlatParameters:
+    def __init__(self, model: torch.nn.Module, device):
+        self.named = [(n, p) for n, p in model.named_parameters() if p.requires_grad and not any(u in n for u in _UNUSED)]
+        self.offsets: Dict[str, int] = {}
+        total = 0
+        for n, p in self.named:
+            self.offsets[n] = total
+            total += (p.numel() + 3) // 4 * 4            # 16-byte aligned views (vectorised GEMM loads)
+        self.numel = total
+        self.params = torch.zeros(total, device=device, dtype=torch.float32)
+        self.grads = torch.zeros(total, device=device, dtype=torch.float32)
+        self.exp_avg = torch.zeros(total, device=device, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(total, device=device, dtype=torch.float32)
+        self.sink = {}
+        for n, p in self.named:
+            o = self.offsets[n]
+            view = self.params[o:o + p.numel()].view_as(p)
+            view.copy_(p.data)
+            p.data = view
+            self.sink[id(p)] = self.grads[o:o + p.numel()].view_as(p)
+
+    def grad_of(self, name: str) -> torch.Tensor:
+        p = dict(self.named)[name]
+        return self.sink[id(p)]
+
+
+class TrainStep:
+    def __init__(self, model, device, lr: float = 1e-5, weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8,
+                 energy_weight: float = 1.0, gradient_weight: float = 0.8, proper_regularisation: float = 1.0,
+                 improper_regularisation: float = 1.0, world_size: int = 1, use_cuda_graph: bool = True,
+                 process_group=None):
+        self.device = torch.device(device)
+        self.model = model.to(self.device).train()
+        self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
+        self.flat = FlatParameters(self.model, self.device)
+        self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
+        self.weights = (energy_weight, gradient_weight, proper_regularisation, improper_regularisation)
+        self.world_size = world_size
+        self.pg = process_group
+        self.use_cuda_graph = use_cuda_graph
+        self.t = 0
+        self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self._static: Dict[tuple, dict] = {}
+        # warm-up and capture both run on this side stream (the whole-network capture recipe of torch.cuda.graphs:
+        # autograd's per-stream state must exist before capture begins)
+        self._side = torch.cuda.Stream(device=self.device) if use_cuda_graph else None
+
+    # ---- one forward + loss + backward on device-resident inputs -------------------------------------------------
+    def _fwd_bwd(self, g):
+        ops.GRAD_SINK = self.flat.sink
+        ops.DropoutSeeds.dev = self.seed_dev
+        try:
+            g = self.energy(self.model(g))
+            plan = get_plan(g)
+            gd, n1 = g.nodes["g"].data, g.nodes["n1"].data
+            loss = ops.MolwiseLossFn.apply(gd["energy"], n1["gradient"], g.nodes["n4"].data["k"], g.nodes["n4_improper"].data["k"],
+                                           gd["energy_ref"], n1["gradient_ref"], gd.get("is_dummy"), plan, self.weights)
+            loss.backward()
+            self.seed_dev.add_(1)
+        finally:
+            ops.GRAD_SINK = None
+            ops.DropoutSeeds.dev = None
+        return loss.detach()
+
+    def _state_for(self, packed: PackedBatch):
+        st = self._static.get(packed.signature)
+        if st is None:
+            st = {"batch": DeviceBatch(packed, self.device), "graph": None, "loss": None, "warm": 0}
+            self._static[packed.signature] = st
+        return st
+
+    def compute_gradients(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
+        """H2D (optional) + forward + loss + backward into the flat gradient buffer.  Returns the device loss."""
+        st = self._state_for(packed)
+        if load:
+            st["batch"].load(packed)
+        g = st["batch"].graph
+        if not self.use_cuda_graph:
+            return self._fwd_bwd(g)
+        if st["graph"] is None:
+            cur = torch.cuda.current_stream(self.device)
+            if st["warm"] < 3:                      # eager warm-up: lazy host constants, smem attributes, allocator
+                st["warm"] += 1
+                self._side.wait_stream(cur)
+                with torch.cuda.stream(self._side):
+                    loss = self._fwd_bwd(g)
+                cur.wait_stream(self._side)
+                return loss
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=self._side):
+                st["loss"] = self._fwd_bwd(g)
+            st["graph"] = graph
+        st["graph"].replay()
+        return st["loss"]
+
+    def all_reduce_gradients(self):
+        if self.world_size > 1:
+            torch.distributed.all_reduce(self.flat.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+
+    def optimizer_step(self):
+        self.t += 1
+        f = self.flat
+        _lib.check(_lib.lib().grappa_adamw(f.numel, ops._p(f.params), ops._p(f.grads), ops._p(f.exp_avg), ops._p(f.exp_avg_sq),
+                                           self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
+                                           1.0 / self.world_size, ops._stream()))
+
+    def step(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
+        loss = self.compute_gradients(packed, load=load)
+        self.all_reduce_gradients()
+        self.optimizer_step()
+        return loss
