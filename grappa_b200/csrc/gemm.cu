@@ -3,17 +3,10 @@
 // Tiling: BMxBN CTA tile, BK-deep k-slices, 256 threads, TMxTN register tile per thread, shared tiles stored
 // k-major ([k][m] / [k][n]) so that the inner product reads float4s without bank conflicts, register-staged
 // double buffering of the global loads.  Algorithmic flops 2MNK.
-#include "common.cuh"
+#include "gemm_common.cuh"
 
 namespace grappa {
 
-struct GemmParams {
-    const float* A; const float* B; float* C;
-    const float* bias; const float* res1; const float* res2;
-    int64_t M, N, K, lda, ldb, ldc, ldr1, ldr2;
-    int act; float drop_p; float drop_scale; uint64_t seed; const uint64_t* seed_dev;
-    int a_vec, b_vec, c_vec;   // 16-byte vector access allowed for A / B / (C, res)
-};
 
 // Element (row r of the tile operand, k) lives at  base[r*ld + k]  (K_CONTIG)  or  base[k*ld + r]  (!K_CONTIG).
 template <int BR, int BK, bool K_CONTIG>
@@ -189,8 +182,6 @@ static int launch_layout(int layout, const GemmParams& p, cudaStream_t st) {
 }
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
-
-int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled);   // gemm_tc.cu
 
 }  // namespace grappa
 

@@ -1,0 +1,17 @@
+// Parameters shared by the FFMA (gemm.cu) and tcgen05 (gemm_tc.cu) GEMM paths.
+#pragma once
+#include "common.cuh"
+
+namespace grappa {
+
+struct GemmParams {
+    const float* A; const float* B; float* C;
+    const float* bias; const float* res1; const float* res2;
+    int64_t M, N, K, lda, ldb, ldc, ldr1, ldr2;
+    int act; float drop_p; float drop_scale; uint64_t seed; const uint64_t* seed_dev;
+    int a_vec, b_vec, c_vec;   // 16-byte vector access allowed for A / B / (C, res)
+};
+
+int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled);   // gemm_tc.cu
+
+}  // namespace grappa

@@ -1,11 +1,391 @@
-// Tensor-core (tcgen05 3xTF32) GEMM path — dispatch stub; falls through to the fp32 FFMA tiles when it declines.
-#include "common.cuh"
+// K2 (tensor-core path, math_mode 1): 3xTF32 GEMM on tcgen05 with the same fused epilogue as gemm.cu.
+//
+//   C[M,N] = epi( sum_k A(m,k) * B(n,k) ),   A = A_hi + A_lo, B = B_hi + B_lo   (hi = top 19 bits, lo = fp32 rest)
+//   D += A_lo*B_hi + A_hi*B_lo + A_hi*B_hi        -> fp32-level accuracy (dropped A_lo*B_lo ~ 2^-22 relative)
+//
+// One CTA per 128x128 output tile, 10 warps:
+//   warp 0   TMA producer: raw fp32 operand tiles (128 rows x 32 k, SWIZZLE_128B) into a 3-stage shared-memory ring
+//   warp 1   MMA issuer: 12 tcgen05.mma (kind::tf32, 128x128x8) per stage, accumulator in TMEM (128 lanes x 128 cols)
+//   warps 2-5  split workers: turn each landed raw tile into (hi in place, lo in a second buffer) — element-wise, so
+//              it is independent of the swizzle
+//   warps 6-9  promote each finished K slice from TMEM into fp32 registers (tcgen05.ld + add) and run the epilogue
+//              (bias / ELU / dropout / residuals -> global)
+// Operands may be K-major (row-major with k contiguous) or MN-major (k-major rows, m/n contiguous); both are
+// described to the tensor core through the shared-memory matrix descriptor, so the three layouts of grappa_gemm
+// (NT / NN / TN) need no transposes.  Out-of-range rows / k are zero-filled by TMA.
+#include "gemm_common.cuh"
+#include <cuda.h>
 
 namespace grappa {
-struct GemmParams;
-int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled) {
-    (void)layout; (void)p; (void)st;
-    *handled = false;
+
+
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 32;
+constexpr int STAGES = 3;
+constexpr int TILE_BYTES = BM * BK * 4;            // 16 KB per operand tile
+constexpr int STAGE_BYTES = 4 * TILE_BYTES;        // A_hi, A_lo, B_hi, B_lo
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int THREADS = 320;
+constexpr uint32_t TMEM_COLS = 512;
+constexpr int KB_PER_CHUNK = 4;                   // K slice of 4 * 32 = 128 per promoted accumulator
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+// shared-memory matrix descriptor (sm_100 version 1); offsets in bytes.
+// layout_type 2 = SWIZZLE_128B (16-byte chunks, 8-row atoms; K-major operands),
+// layout_type 1 = SWIZZLE_128B_BASE32B (32-byte chunks, 4-row atoms): the only layout tcgen05 accepts for MN-major
+// 32-bit operands; the matching TMA mode is CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;     // descriptor version (Blackwell)
+    d |= (uint64_t)layout_type << 61;
+    return d;
+}
+
+// round-to-nearest fp32 -> tf32 (low 13 mantissa bits zero): unbiased split errors, exact operands for the tensor core
+__device__ __forceinline__ float tf32_rn(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+
+// A_MN / B_MN: operand is MN-major (rows of the global matrix run along k, m/n contiguous)
+//
+// Accumulation precision: the tensor core adds into its fp32 accumulator with truncation, which biases long sums
+// (measured: relative error ~6e-8 per MMA, i.e. 1e-5 at K = 512 with 3 MMAs per k-step).  Therefore
+//   - the hi*hi products of each K_CHUNK = 128 slice go to one of two ping-pong TMEM accumulators (16 MMAs each) and are
+//     promoted into fp32 registers (round-to-nearest adds) by the accumulate warps while the next slice is running;
+//   - the small cross terms A_lo*B_hi + A_hi*B_lo accumulate in a third TMEM region over the whole K range (their
+//     truncation error is 2^-11 smaller) and are added once at the end.
+template <bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* full = bars;                       // TMA landed                    (count 1 + tx bytes)
+    uint64_t* split = bars + STAGES;             // hi/lo tiles are ready         (count 128)
+    uint64_t* empty = bars + 2 * STAGES;         // MMAs of the stage done        (count 1, via tcgen05.commit)
+    uint64_t* chunk_full = bars + 3 * STAGES;    // [2] slice accumulator complete (count 1, via tcgen05.commit)
+    uint64_t* chunk_empty = bars + 3 * STAGES + 2;   // [2] slice accumulator drained (count 128)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int nk = (int)((p.K + BK - 1) / BK);
+    const int n_chunks = (nk + KB_PER_CHUNK - 1) / KB_PER_CHUNK;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&split[s], 128); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&chunk_full[b], 1); mbar_init(&chunk_empty[b], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;       // columns [0,128) and [128,256): slice accumulators, [256,384): cross terms
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % STAGES;
+                if (kb >= STAGES) mbar_wait(&empty[s], ((kb / STAGES) - 1) & 1);
+                uint8_t* st = smem + s * STAGE_BYTES;
+                mbar_expect_tx(&full[s], 2 * TILE_BYTES);
+                const int k0 = kb * BK;
+                if (!A_MN) {
+                    tma_load_2d(st, &mapA, &full[s], k0, m0);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BM / 32; ++j) tma_load_2d(st + j * (BK * 128), &mapA, &full[s], m0 + 32 * j, k0);
+                }
+                if (!B_MN) {
+                    tma_load_2d(st + 2 * TILE_BYTES, &mapB, &full[s], k0, n0);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < BN / 32; ++j) tma_load_2d(st + 2 * TILE_BYTES + j * (BK * 128), &mapB, &full[s], n0 + 32 * j, k0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            // instruction descriptor: D=F32, A=B=TF32, majors, N>>3 at [17,23), M>>4 at [24,29)
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t tmem_cross = tmem_base + 2 * BN;
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % STAGES;
+                const int chunk = kb / KB_PER_CHUNK, buf = chunk & 1;
+                const bool chunk_start = (kb % KB_PER_CHUNK) == 0;
+                if (chunk_start && chunk >= 2) {
+                    mbar_wait(&chunk_empty[buf], ((chunk >> 1) - 1) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                mbar_wait(&split[s], (kb / STAGES) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES), a_lo = a_hi + TILE_BYTES;
+                const uint32_t b_hi = a_hi + 2 * TILE_BYTES, b_lo = a_hi + 3 * TILE_BYTES;
+                const uint32_t tmem_main = tmem_base + buf * BN;
+#pragma unroll
+                for (int k = 0; k < BK / 8; ++k) {
+                    // K-major: 32 bytes per k-step inside the 128-byte swizzle row, 8-row groups 1024 B apart (SBO).
+                    // MN-major: 8 k-rows (two 4-row atoms, SBO = 512 B) per k-step, 32-wide m/n atoms BK*128 B apart (LBO).
+                    const uint32_t ao = A_MN ? k * 1024 : k * 32, bo = B_MN ? k * 1024 : k * 32;
+                    const uint32_t a_lbo = A_MN ? BK * 128 : 16, b_lbo = B_MN ? BK * 128 : 16;
+                    const uint32_t a_sbo = A_MN ? 512 : 1024, b_sbo = B_MN ? 512 : 1024;
+                    const uint32_t a_lt = A_MN ? 1 : 2, b_lt = B_MN ? 1 : 2;
+                    const uint64_t dah = make_desc(a_hi + ao, a_lbo, a_sbo, a_lt), dal = make_desc(a_lo + ao, a_lbo, a_sbo, a_lt);
+                    const uint64_t dbh = make_desc(b_hi + bo, b_lbo, b_sbo, b_lt), dbl = make_desc(b_lo + bo, b_lbo, b_sbo, b_lt);
+                    umma_tf32(tmem_cross, dal, dbh, idesc, (kb | k) != 0);
+                    umma_tf32(tmem_cross, dah, dbl, idesc, 1);
+                    umma_tf32(tmem_main, dah, dbh, idesc, !(chunk_start && k == 0));
+                }
+                umma_commit(&empty[s]);          // frees the stage once these MMAs have read it
+                if ((kb % KB_PER_CHUNK) == KB_PER_CHUNK - 1 || kb == nk - 1) umma_commit(&chunk_full[buf]);
+            }
+        }
+    } else if (warp < 6) {
+        // ------------------------------------------------------------------ split workers (warps 2..5)
+        const int wt = threadIdx.x - 64;          // 0..127
+        for (int kb = 0; kb < nk; ++kb) {
+            const int s = kb % STAGES;
+            mbar_wait(&full[s], (kb / STAGES) & 1);
+            uint8_t* st = smem + s * STAGE_BYTES;
+#pragma unroll
+            for (int op = 0; op < 2; ++op) {
+                float4* hi = reinterpret_cast<float4*>(st + op * 2 * TILE_BYTES);
+                float4* lo = reinterpret_cast<float4*>(st + op * 2 * TILE_BYTES + TILE_BYTES);
+#pragma unroll
+                for (int i = 0; i < TILE_BYTES / 16 / 128; ++i) {
+                    const int o = wt + i * 128;
+                    const float4 x = hi[o];
+                    float4 h, l;
+                    h.x = tf32_rn(x.x); l.x = tf32_rn(x.x - h.x);
+                    h.y = tf32_rn(x.y); l.y = tf32_rn(x.y - h.y);
+                    h.z = tf32_rn(x.z); l.z = tf32_rn(x.z - h.z);
+                    h.w = tf32_rn(x.w); l.w = tf32_rn(x.w - h.w);
+                    hi[o] = h;
+                    lo[o] = l;
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
+            mbar_arrive(&split[s]);
+        }
+    } else {
+        // ------------------------------------------------------------------ accumulate + epilogue (warps 6..9)
+        const int q = warp & 3;                    // TMEM lane quarter this warp may access
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        float acc[BN];
+#pragma unroll
+        for (int j = 0; j < BN; ++j) acc[j] = 0.f;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int buf = c & 1;
+            mbar_wait(&chunk_full[buf], (c >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int cb = 0; cb < BN / 32; ++cb) {
+                uint32_t r[32];
+                tmem_ld32(tmem_base + lane_addr + (uint32_t)(buf * BN + cb * 32), r);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[cb * 32 + j] += __uint_as_float(r[j]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&chunk_empty[buf]);
+        }
+        // cross terms (complete once the last slice's commit has fired)
+#pragma unroll
+        for (int cb = 0; cb < BN / 32; ++cb) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + lane_addr + (uint32_t)(2 * BN + cb * 32), r);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[cb * 32 + j] += __uint_as_float(r[j]);
+        }
+        const int64_t m = (int64_t)m0 + q * 32 + lane;
+        const bool has_drop = p.drop_p > 0.f;
+        const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
+        if (m < p.M) {
+#pragma unroll
+            for (int j4 = 0; j4 < BN / 4; ++j4) {
+                const int64_t n = (int64_t)n0 + j4 * 4;
+                if (n < p.N) {
+                    const int nvalid = (int)min((int64_t)4, p.N - n);
+                    float v[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        float z = acc[j4 * 4 + j];
+                        if (j < nvalid) {
+                            if (p.bias) z += __ldg(p.bias + n + j);
+                            if (p.act == 1) z = elu1(z);
+                            if (has_drop) z = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? z * p.drop_scale : 0.f;
+                            if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n + j);
+                            if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n + j);
+                        }
+                        v[j] = z;
+                    }
+                    float* cp = p.C + m * p.ldc + n;
+                    if (p.c_vec && nvalid == 4) {
+                        *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (j < nvalid) cp[j] = v[j];
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// 2-D fp32 tensor map over a row-major (rows x cols, leading dimension ld) matrix with box (box_cols x box_rows)
+static bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows,
+                     bool mn_major) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 4};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+               CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <bool A_MN, bool B_MN>
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        GRAPPA_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        configured = true;
+    }
+    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM));
+    gemm_tc_kernel<A_MN, B_MN><<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p);
+    GRAPPA_CHECK_LAUNCH();
     return 0;
 }
+
+}  // namespace tc
+
+// Returns handled = false when the shape is not worth / not eligible for the tensor-core path
+// (TMA needs 16-byte aligned bases and row strides; tiny N or K stay on the FFMA tiles).
+int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled) {
+    *handled = false;
+    if (!p.a_vec || !p.b_vec) return 0;
+    if (p.N < 32 || p.K < 32 || p.M < 32) return 0;
+    if (p.M > 2147483647LL / 4 || p.N > 2147483647LL / 4 || p.K > 2147483647LL / 4) return 0;
+    CUtensorMap ma, mb;
+    bool ok;
+    if (layout == 0) {            // A (M,K) k-major, B (N,K) k-major
+        ok = tc::make_map(&ma, p.A, p.M, p.K, p.lda, tc::BK, tc::BM, false) && tc::make_map(&mb, p.B, p.N, p.K, p.ldb, tc::BK, tc::BN, false);
+    } else if (layout == 1) {     // A (M,K) k-major, B stored (K,N): n contiguous
+        ok = tc::make_map(&ma, p.A, p.M, p.K, p.lda, tc::BK, tc::BM, false) && tc::make_map(&mb, p.B, p.K, p.N, p.ldb, 32, tc::BK, true);
+    } else {                      // A stored (K,M): m contiguous, B stored (K,N): n contiguous
+        ok = tc::make_map(&ma, p.A, p.K, p.M, p.lda, 32, tc::BK, true) && tc::make_map(&mb, p.B, p.K, p.N, p.ldb, 32, tc::BK, true);
+    }
+    if (!ok) return 0;
+    int rc;
+    if (layout == 0) rc = tc::launch<false, false>(ma, mb, p, st);
+    else if (layout == 1) rc = tc::launch<false, true>(ma, mb, p, st);
+    else rc = tc::launch<true, true>(ma, mb, p, st);
+    if (rc) return rc;
+    *handled = true;
+    return 0;
+}
+
 }  // namespace grappa

@@ -11,7 +11,8 @@ import torch
 
 from . import _lib
 
-MATH_MODE = 0          # 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm)
+import os as _os
+MATH_MODE = int(_os.environ.get("GRAPPA_MATH_MODE", "1"))   # 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm)
 ACT_NONE, ACT_ELU = 0, 1
 # Optional {id(parameter): gradient buffer}: backward kernels write parameter gradients straight into these buffers
 # (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
