@@ -19,7 +19,7 @@ PROTOTYPES = {
     "grappa_last_error": (c_char_p, []),
     "grappa_abi_version": (I, []),
     "grappa_launch_count": (I64, []),
-    "grappa_gemm": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P]),
+    "grappa_gemm": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P]),
     "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P]),
     "grappa_colsum_scratch_floats": (I64, [I64, I64]),
     "grappa_colsum": (I, [I64, I64, P, I64, P, P, P]),

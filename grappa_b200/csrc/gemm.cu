@@ -190,7 +190,8 @@ using namespace grappa;
 extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
                            const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                            const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
-                           float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode, void* stream) {
+                           float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                           float* workspace, int64_t workspace_floats, void* stream) {
     GRAPPA_CHECK_ARG(layout >= 0 && layout <= 2, "layout must be 0 (NT), 1 (NN) or 2 (TN)");
     GRAPPA_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "negative size");
     GRAPPA_CHECK_ARG(act == 0 || act == 1, "act must be 0 (none) or 1 (ELU)");
@@ -208,7 +209,7 @@ extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
     cudaStream_t st = (cudaStream_t)stream;
     if (math_mode == 1) {
         bool handled = false;
-        int rc = gemm_tc_dispatch(layout, p, st, &handled);
+        int rc = gemm_tc_dispatch(layout, p, st, workspace, workspace_floats, &handled);
         if (rc) return rc;
         if (handled) return 0;
     }

@@ -12,6 +12,7 @@ struct GemmParams {
     int a_vec, b_vec, c_vec;   // 16-byte vector access allowed for A / B / (C, res)
 };
 
-int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled);   // gemm_tc.cu
+int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
+                     bool* handled);   // gemm_tc.cu
 
 }  // namespace grappa

@@ -28,6 +28,7 @@ constexpr int STAGE_BYTES = 4 * TILE_BYTES;        // A_hi, A_lo, B_hi, B_lo
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int THREADS = 320;
 constexpr uint32_t TMEM_COLS = 512;
+constexpr int EPI_LD = BN + 4;                     // padded row stride of the epilogue staging tile (conflict-free float4)
 constexpr int KB_PER_CHUNK = 4;                   // K slice of 4 * 32 = 128 per promoted accumulator
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -123,7 +124,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 //     truncation error is 2^-11 smaller) and are added once at the end.
 template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmParams p,
+               int kb_per_split, float* __restrict__ partial) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
@@ -136,7 +138,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    const int nk = (int)((p.K + BK - 1) / BK);
+    // split-K: blockIdx.z owns k-blocks [kb_begin, kb_begin + nk); partial sums go to `partial` without an epilogue
+    const int nk_total = (int)((p.K + BK - 1) / BK);
+    const int kb_begin = blockIdx.z * kb_per_split;
+    const int nk = min(kb_per_split, nk_total - kb_begin);
     const int n_chunks = (nk + KB_PER_CHUNK - 1) / KB_PER_CHUNK;
 
     if (threadIdx.x == 0) {
@@ -161,7 +166,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                 if (kb >= STAGES) mbar_wait(&empty[s], ((kb / STAGES) - 1) & 1);
                 uint8_t* st = smem + s * STAGE_BYTES;
                 mbar_expect_tx(&full[s], 2 * TILE_BYTES);
-                const int k0 = kb * BK;
+                const int k0 = (kb_begin + kb) * BK;
                 if (!A_MN) {
                     tma_load_2d(st, &mapA, &full[s], k0, m0);
                 } else {
@@ -272,38 +277,75 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 32; ++j) acc[cb * 32 + j] += __uint_as_float(r[j]);
         }
-        const int64_t m = (int64_t)m0 + q * 32 + lane;
+        // Coalesced epilogue: every thread owns one accumulator ROW, so writing it out directly would touch 32
+        // different rows per warp instruction.  Stage the tile in shared memory (all pipeline stages are idle once the
+        // last slice has been committed), then let each warp stream whole rows: 512 contiguous bytes per instruction.
+        float* tile = reinterpret_cast<float*>(smem);                     // [128][EPI_LD]
+        {
+            float* row = tile + (q * 32 + lane) * EPI_LD;
+#pragma unroll
+            for (int j4 = 0; j4 < BN / 4; ++j4)
+                *reinterpret_cast<float4*>(row + j4 * 4) = make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");                    // the four accumulate warps only
+        if (partial != nullptr) {
+            float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
+            const int64_t nn = (int64_t)n0 + lane * 4;
+            const int nv = (int)max((int64_t)0, min((int64_t)4, p.N - nn));
+            const bool vec = (p.N % 4 == 0);
+            for (int it = 0; it < BM / 4; ++it) {
+                const int r = it * 4 + (warp - 6);
+                const int64_t m = (int64_t)m0 + r;
+                if (m >= p.M || nv == 0) continue;
+                const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+                float* cp = dst + m * p.N + nn;
+                if (vec && nv == 4) *reinterpret_cast<float4*>(cp) = a4;
+                else { const float v[4] = {a4.x, a4.y, a4.z, a4.w}; for (int j = 0; j < nv; ++j) cp[j] = v[j]; }
+            }
+        } else {
         const bool has_drop = p.drop_p > 0.f;
         const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
-        if (m < p.M) {
+        const int ew = warp - 6;
+        const int64_t n = (int64_t)n0 + lane * 4;
+        const int nvalid = (int)max((int64_t)0, min((int64_t)4, p.N - n));
+        float bv[4] = {0.f, 0.f, 0.f, 0.f};
+        if (p.bias) {
 #pragma unroll
-            for (int j4 = 0; j4 < BN / 4; ++j4) {
-                const int64_t n = (int64_t)n0 + j4 * 4;
-                if (n < p.N) {
-                    const int nvalid = (int)min((int64_t)4, p.N - n);
-                    float v[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        float z = acc[j4 * 4 + j];
-                        if (j < nvalid) {
-                            if (p.bias) z += __ldg(p.bias + n + j);
-                            if (p.act == 1) z = elu1(z);
-                            if (has_drop) z = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? z * p.drop_scale : 0.f;
-                            if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n + j);
-                            if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n + j);
-                        }
-                        v[j] = z;
-                    }
-                    float* cp = p.C + m * p.ldc + n;
-                    if (p.c_vec && nvalid == 4) {
-                        *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (j < nvalid) cp[j] = v[j];
-                    }
-                }
+            for (int j = 0; j < 4; ++j)
+                if (j < nvalid) bv[j] = __ldg(p.bias + n + j);
+        }
+        const bool vec_res1 = p.res1 && nvalid == 4 && (p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0);
+        const bool vec_res2 = p.res2 && nvalid == 4 && (p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0);
+#pragma unroll 4
+        for (int it = 0; it < BM / 4; ++it) {
+            const int r = it * 4 + ew;
+            const int64_t m = (int64_t)m0 + r;
+            if (m >= p.M || nvalid == 0) continue;
+            const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+            float v[4] = {a4.x, a4.y, a4.z, a4.w};
+            float r1[4] = {0.f, 0.f, 0.f, 0.f}, r2[4] = {0.f, 0.f, 0.f, 0.f};
+            if (p.res1) {
+                if (vec_res1) { const float4 t = __ldg(reinterpret_cast<const float4*>(p.res1 + m * p.ldr1 + n)); r1[0] = t.x; r1[1] = t.y; r1[2] = t.z; r1[3] = t.w; }
+                else { for (int j = 0; j < nvalid; ++j) r1[j] = __ldg(p.res1 + m * p.ldr1 + n + j); }
             }
+            if (p.res2) {
+                if (vec_res2) { const float4 t = __ldg(reinterpret_cast<const float4*>(p.res2 + m * p.ldr2 + n)); r2[0] = t.x; r2[1] = t.y; r2[2] = t.z; r2[3] = t.w; }
+                else { for (int j = 0; j < nvalid; ++j) r2[j] = __ldg(p.res2 + m * p.ldr2 + n + j); }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float z = v[j] + bv[j];
+                if (p.act == 1) z = elu1(z);
+                if (has_drop) z = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? z * p.drop_scale : 0.f;
+                v[j] = z + r1[j] + r2[j];
+            }
+            float* cp = p.C + m * p.ldc + n;
+            if (p.c_vec && nvalid == 4) {
+                *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+                for (int j = 0; j < nvalid; ++j) cp[j] = v[j];
+            }
+        }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -311,6 +353,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// split-K reduction: C = epilogue( sum_z partial[z] ), fixed summation order (deterministic)
+__global__ void splitk_reduce_kernel(GemmParams p, int splits, const float* __restrict__ partial) {
+    const int64_t total = p.M * p.N;
+    const bool has_drop = p.drop_p > 0.f;
+    const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t m = i / p.N, n = i % p.N;
+        float z = 0.f;
+        for (int s = 0; s < splits; ++s) z += partial[(int64_t)s * total + i];
+        if (p.bias) z += __ldg(p.bias + n);
+        if (p.act == 1) z = elu1(z);
+        if (has_drop) z = hash_uniform(seed, (uint64_t)i) >= p.drop_p ? z * p.drop_scale : 0.f;
+        if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n);
+        if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n);
+        p.C[m * p.ldc + n] = z;
     }
 }
 
@@ -348,15 +408,35 @@ static bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t 
 }
 
 template <bool A_MN, bool B_MN>
-static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st) {
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, cudaStream_t st, float* workspace,
+                  int64_t workspace_floats) {
     static bool configured = false;
     if (!configured) {
         GRAPPA_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         configured = true;
     }
-    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM));
-    gemm_tc_kernel<A_MN, B_MN><<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p);
+    const int64_t tiles = ceil_div(p.N, BN) * ceil_div(p.M, BM);
+    const int nk = (int)ceil_div(p.K, BK);
+    // split K when the tile grid leaves most of the 148 SMs idle and the k loop is long enough to amortise the
+    // extra pass; slices are multiples of the promotion chunk
+    int splits = 1;
+    if (workspace != nullptr && tiles <= 74 && nk >= 32) {
+        const int want = (int)std::min<int64_t>(ceil_div(148, tiles), nk / 16);
+        if (want > 1 && (int64_t)want * p.M * p.N <= workspace_floats) splits = want;
+    }
+    int kps = nk;
+    if (splits > 1) {
+        kps = (int)ceil_div(ceil_div(nk, splits), KB_PER_CHUNK) * KB_PER_CHUNK;
+        splits = (int)ceil_div(nk, kps);
+    }
+    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM), (unsigned)splits);
+    gemm_tc_kernel<A_MN, B_MN><<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, p, kps, splits > 1 ? workspace : nullptr);
     GRAPPA_CHECK_LAUNCH();
+    if (splits > 1) {
+        const int64_t total = p.M * p.N;
+        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8), 256, 0, st>>>(p, splits, workspace);
+        GRAPPA_CHECK_LAUNCH();
+    }
     return 0;
 }
 
@@ -364,7 +444,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
 
 // Returns handled = false when the shape is not worth / not eligible for the tensor-core path
 // (TMA needs 16-byte aligned bases and row strides; tiny N or K stay on the FFMA tiles).
-int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* handled) {
+int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats, bool* handled) {
     *handled = false;
     if (!p.a_vec || !p.b_vec) return 0;
     if (p.N < 32 || p.K < 32 || p.M < 32) return 0;
@@ -380,9 +460,9 @@ int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, bool* han
     }
     if (!ok) return 0;
     int rc;
-    if (layout == 0) rc = tc::launch<false, false>(ma, mb, p, st);
-    else if (layout == 1) rc = tc::launch<false, true>(ma, mb, p, st);
-    else rc = tc::launch<true, true>(ma, mb, p, st);
+    if (layout == 0) rc = tc::launch<false, false>(ma, mb, p, st, workspace, workspace_floats);
+    else if (layout == 1) rc = tc::launch<false, true>(ma, mb, p, st, workspace, workspace_floats);
+    else rc = tc::launch<true, true>(ma, mb, p, st, workspace, workspace_floats);
     if (rc) return rc;
     *handled = true;
     return 0;

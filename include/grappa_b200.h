@@ -40,11 +40,14 @@ int64_t grappa_launch_count(void);
  * counter-based hash of (seed + *seed_dev, row*N+col), kept values scaled by 1/(1-p).  seed_dev (device, may be
  * NULL) lets a captured CUDA graph draw fresh masks on every replay: the step driver bumps it between steps.
  * math_mode: 0 = fp32 FFMA tiles, 1 = tcgen05 3xTF32 (split-precision tensor-core tiles, fp32-level accuracy).
+ * workspace (may be NULL): caller-provided scratch of workspace_floats floats; lets the tensor-core path split the k
+ * range over several CTAs when the output has few tiles (weight gradients), reduced in fixed order.
  */
 int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
                 const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                 const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
-                float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode, void* stream);
+                float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                float* workspace, int64_t workspace_floats, void* stream);
 
 /* dZ = dY * keepmask/(1-p) * act'(.) where the activation output is recovered as (Y - res1 - res2)*(1-p).
  * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL. */

@@ -61,7 +61,7 @@ def test_loader_and_error_string():
     L = _lib.lib()
     assert L.grappa_abi_version() == 1
     # argument validation happens on the host before any launch: usable without a GPU
-    rc = L.grappa_gemm(7, 1, 1, 1, None, 1, None, 1, None, 1, None, 0, None, 0, None, 0, 0.0, 0, None, 0, None)
+    rc = L.grappa_gemm(7, 1, 1, 1, None, 1, None, 1, None, 1, None, 0, None, 0, None, 0, 0.0, 0, None, 0, None, 0, None)
     assert rc != 0
     assert b"layout" in L.grappa_last_error()
     with pytest.raises(_lib.GrappaKernelError):
