@@ -31,6 +31,20 @@ constexpr uint32_t TMEM_COLS = 512;
 constexpr int EPI_LD = BN + 4;                     // padded row stride of the epilogue staging tile (conflict-free float4)
 constexpr int KB_PER_CHUNK = 4;                   // K slice of 4 * 32 = 128 per promoted accumulator
 
+#ifdef GRAPPA_GEMM_TIMELINE
+__device__ unsigned long long g_timeline[16];
+__device__ __forceinline__ void stamp(int i) {
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        g_timeline[i] = t;
+    }
+}
+#define STAMP(i, cond) do { if (cond) stamp(i); } while (0)
+#else
+#define STAMP(i, cond) do {} while (0)
+#endif
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -137,6 +151,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    STAMP(0, threadIdx.x == 0);
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
     // split-K: blockIdx.z owns k-blocks [kb_begin, kb_begin + nk); partial sums go to `partial` without an epilogue
     const int nk_total = (int)((p.K + BK - 1) / BK);
@@ -156,6 +171,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    STAMP(1, threadIdx.x == 0);
     const uint32_t tmem_base = *tmem_slot;       // columns [0,128) and [128,256): slice accumulators, [256,384): cross terms
 
     if (warp == 0) {
@@ -225,6 +241,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int kb = 0; kb < nk; ++kb) {
             const int s = kb % STAGES;
             mbar_wait(&full[s], (kb / STAGES) & 1);
+            STAMP(2, threadIdx.x == 64 && kb == 0);
             uint8_t* st = smem + s * STAGE_BYTES;
 #pragma unroll
             for (int op = 0; op < 2; ++op) {
@@ -256,6 +273,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int c = 0; c < n_chunks; ++c) {
             const int buf = c & 1;
             mbar_wait(&chunk_full[buf], (c >> 1) & 1);
+            STAMP(3, threadIdx.x == 192 && c == 0);
+            STAMP(4, threadIdx.x == 192 && c == n_chunks - 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
             for (int cb = 0; cb < BN / 32; ++cb) {
@@ -280,6 +299,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // Coalesced epilogue: every thread owns one accumulator ROW, so writing it out directly would touch 32
         // different rows per warp instruction.  Stage the tile in shared memory (all pipeline stages are idle once the
         // last slice has been committed), then let each warp stream whole rows: 512 contiguous bytes per instruction.
+        STAMP(5, threadIdx.x == 192);
         float* tile = reinterpret_cast<float*>(smem);                     // [128][EPI_LD]
         {
             float* row = tile + (q * 32 + lane) * EPI_LD;
@@ -287,69 +307,114 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             for (int j4 = 0; j4 < BN / 4; ++j4)
                 *reinterpret_cast<float4*>(row + j4 * 4) = make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]);
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");                    // the four accumulate warps only
-        if (partial != nullptr) {
-            float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
-            const int64_t nn = (int64_t)n0 + lane * 4;
-            const int nv = (int)max((int64_t)0, min((int64_t)4, p.N - nn));
-            const bool vec = (p.N % 4 == 0);
-            for (int it = 0; it < BM / 4; ++it) {
-                const int r = it * 4 + (warp - 6);
-                const int64_t m = (int64_t)m0 + r;
-                if (m >= p.M || nv == 0) continue;
-                const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
-                float* cp = dst + m * p.N + nn;
-                if (vec && nv == 4) *reinterpret_cast<float4*>(cp) = a4;
-                else { const float v[4] = {a4.x, a4.y, a4.z, a4.w}; for (int j = 0; j < nv; ++j) cp[j] = v[j]; }
-            }
-        } else {
-        const bool has_drop = p.drop_p > 0.f;
-        const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
-        const int ew = warp - 6;
+    }
+    // ---------------------------------------------------------------------- write-out: all ten warps
+    // The accumulate warps have staged the tile; every other role has drained its loop.  One CTA-wide barrier, then
+    // each warp streams whole rows (512 contiguous bytes per instruction), four rows in flight per iteration.
+    __syncthreads();
+    STAMP(6, threadIdx.x == 192);
+    {
+        const float* tile = reinterpret_cast<const float*>(smem);
         const int64_t n = (int64_t)n0 + lane * 4;
         const int nvalid = (int)max((int64_t)0, min((int64_t)4, p.N - n));
-        float bv[4] = {0.f, 0.f, 0.f, 0.f};
-        if (p.bias) {
+        constexpr int RPI = 4;
+        if (partial != nullptr) {
+            float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
+            const bool vec = (p.N % 4 == 0);
+            for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (j < nvalid) bv[j] = __ldg(p.bias + n + j);
-        }
-        const bool vec_res1 = p.res1 && nvalid == 4 && (p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0);
-        const bool vec_res2 = p.res2 && nvalid == 4 && (p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0);
-#pragma unroll 4
-        for (int it = 0; it < BM / 4; ++it) {
-            const int r = it * 4 + ew;
-            const int64_t m = (int64_t)m0 + r;
-            if (m >= p.M || nvalid == 0) continue;
-            const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
-            float v[4] = {a4.x, a4.y, a4.z, a4.w};
-            float r1[4] = {0.f, 0.f, 0.f, 0.f}, r2[4] = {0.f, 0.f, 0.f, 0.f};
-            if (p.res1) {
-                if (vec_res1) { const float4 t = __ldg(reinterpret_cast<const float4*>(p.res1 + m * p.ldr1 + n)); r1[0] = t.x; r1[1] = t.y; r1[2] = t.z; r1[3] = t.w; }
-                else { for (int j = 0; j < nvalid; ++j) r1[j] = __ldg(p.res1 + m * p.ldr1 + n + j); }
+                for (int i = 0; i < RPI; ++i) {
+                    const int r = r0 + i;
+                    const int64_t m = (int64_t)m0 + r;
+                    if (r >= BM || m >= p.M || nvalid == 0) continue;
+                    const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+                    float* cp = dst + m * p.N + n;
+                    if (vec && nvalid == 4) {
+                        *reinterpret_cast<float4*>(cp) = a4;
+                    } else {
+                        if (nvalid > 0) cp[0] = a4.x;
+                        if (nvalid > 1) cp[1] = a4.y;
+                        if (nvalid > 2) cp[2] = a4.z;
+                        if (nvalid > 3) cp[3] = a4.w;
+                    }
+                }
             }
-            if (p.res2) {
-                if (vec_res2) { const float4 t = __ldg(reinterpret_cast<const float4*>(p.res2 + m * p.ldr2 + n)); r2[0] = t.x; r2[1] = t.y; r2[2] = t.z; r2[3] = t.w; }
-                else { for (int j = 0; j < nvalid; ++j) r2[j] = __ldg(p.res2 + m * p.ldr2 + n + j); }
+        } else {
+            const bool has_drop = p.drop_p > 0.f;
+            const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.bias) {
+                if (nvalid > 0) bv.x = __ldg(p.bias + n);
+                if (nvalid > 1) bv.y = __ldg(p.bias + n + 1);
+                if (nvalid > 2) bv.z = __ldg(p.bias + n + 2);
+                if (nvalid > 3) bv.w = __ldg(p.bias + n + 3);
             }
+            const bool vec_res1 = p.res1 && nvalid == 4 && (p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0);
+            const bool vec_res2 = p.res2 && nvalid == 4 && (p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0);
+            for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
+                float4 a4[RPI], q1[RPI], q2[RPI];
+                bool ok[RPI];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float z = v[j] + bv[j];
-                if (p.act == 1) z = elu1(z);
-                if (has_drop) z = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? z * p.drop_scale : 0.f;
-                v[j] = z + r1[j] + r2[j];
+                for (int i = 0; i < RPI; ++i) {           // issue all loads of the four rows first
+                    const int r = r0 + i;
+                    const int64_t m = (int64_t)m0 + r;
+                    ok[i] = r < BM && m < p.M && nvalid > 0;
+                    a4[i] = q1[i] = q2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (!ok[i]) continue;
+                    a4[i] = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+                    if (p.res1) {
+                        const float* rp = p.res1 + m * p.ldr1 + n;
+                        if (vec_res1) q1[i] = __ldg(reinterpret_cast<const float4*>(rp));
+                        else {
+                            q1[i].x = __ldg(rp);
+                            if (nvalid > 1) q1[i].y = __ldg(rp + 1);
+                            if (nvalid > 2) q1[i].z = __ldg(rp + 2);
+                            if (nvalid > 3) q1[i].w = __ldg(rp + 3);
+                        }
+                    }
+                    if (p.res2) {
+                        const float* rp = p.res2 + m * p.ldr2 + n;
+                        if (vec_res2) q2[i] = __ldg(reinterpret_cast<const float4*>(rp));
+                        else {
+                            q2[i].x = __ldg(rp);
+                            if (nvalid > 1) q2[i].y = __ldg(rp + 1);
+                            if (nvalid > 2) q2[i].z = __ldg(rp + 2);
+                            if (nvalid > 3) q2[i].w = __ldg(rp + 3);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < RPI; ++i) {
+                    if (!ok[i]) continue;
+                    const int64_t m = (int64_t)m0 + r0 + i;
+                    float v[4] = {a4[i].x + bv.x, a4[i].y + bv.y, a4[i].z + bv.z, a4[i].w + bv.w};
+                    if (p.act == 1) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) v[j] = elu1(v[j]);
+                    }
+                    if (has_drop) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            v[j] = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? v[j] * p.drop_scale : 0.f;
+                    }
+                    v[0] = (v[0] + q1[i].x) + q2[i].x; v[1] = (v[1] + q1[i].y) + q2[i].y; v[2] = (v[2] + q1[i].z) + q2[i].z; v[3] = (v[3] + q1[i].w) + q2[i].w;
+                    float* cp = p.C + m * p.ldc + n;
+                    if (p.c_vec && nvalid == 4) {
+                        *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+                    } else {
+                        if (nvalid > 0) cp[0] = v[0];
+                        if (nvalid > 1) cp[1] = v[1];
+                        if (nvalid > 2) cp[2] = v[2];
+                        if (nvalid > 3) cp[3] = v[3];
+                    }
+                }
             }
-            float* cp = p.C + m * p.ldc + n;
-            if (p.c_vec && nvalid == 4) {
-                *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
-                for (int j = 0; j < nvalid; ++j) cp[j] = v[j];
-            }
-        }
         }
     }
+    STAMP(7, threadIdx.x == 192);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    STAMP(8, threadIdx.x == 0);
     if (warp == 1) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
@@ -469,3 +534,9 @@ int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* wo
 }
 
 }  // namespace grappa
+
+#ifdef GRAPPA_GEMM_TIMELINE
+extern "C" int grappa_debug_timeline(unsigned long long* out) {
+    return cudaMemcpyFromSymbol(out, grappa::tc::g_timeline, sizeof(unsigned long long) * 16) == cudaSuccess ? 0 : 1;
+}
+#endif

@@ -25,7 +25,12 @@ def _stream():
 
 
 def _p(t: Optional[torch.Tensor]):
-    return None if t is None else ctypes.c_void_p(t.data_ptr())
+    if t is None:
+        return None
+    prof = _lib.profiler
+    if prof is not None:
+        prof.keepalive.append(t)      # recorded launches are replayed later: their buffers must stay allocated
+    return ctypes.c_void_p(t.data_ptr())
 
 
 def _req(t: torch.Tensor, name: str, dtype=torch.float32):
