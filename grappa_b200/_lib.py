@@ -20,7 +20,7 @@ PROTOTYPES = {
     "grappa_abi_version": (I, []),
     "grappa_launch_count": (I64, []),
     "grappa_gemm": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P]),
-    "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P]),
+    "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P, P, P]),
     "grappa_colsum_scratch_floats": (I64, [I64, I64]),
     "grappa_colsum": (I, [I64, I64, P, I64, P, P, P]),
     "grappa_layernorm_fwd": (I, [I64, I64, P, I64, P, P, P, I64, P, P, P]),

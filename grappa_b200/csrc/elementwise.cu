@@ -10,7 +10,9 @@ namespace grappa {
 
 constexpr float kLnEps = 1e-5f;
 
-// one warp per row; the row (<= 8 KB) stays L1-resident across the three passes
+// one warp per row; the row (<= 8 KB) stays L1-resident across the three passes.  VEC: float4 accesses
+// (D % 4 == 0, leading dimensions % 4 == 0, 16-byte aligned bases), 512 contiguous bytes per warp instruction.
+template <bool VEC>
 __global__ void __launch_bounds__(256) layernorm_fwd_kernel(int64_t M, int D, const float* __restrict__ X, int64_t ldx,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
                                                             float* __restrict__ Y, int64_t ldy, float* __restrict__ mean,
@@ -19,17 +21,39 @@ __global__ void __launch_bounds__(256) layernorm_fwd_kernel(int64_t M, int D, co
     const int lane = threadIdx.x & 31;
     if (row >= M) return;
     const float* x = X + row * ldx;
-    float s = 0.f;
-    for (int i = lane; i < D; i += 32) s += x[i];
-    const float mu = warp_sum(s) / (float)D;
-    float v = 0.f;
-    for (int i = lane; i < D; i += 32) { const float d = x[i] - mu; v = fmaf(d, d, v); }
-    const float rs = rsqrtf(warp_sum(v) / (float)D + kLnEps);
     float* y = Y + row * ldy;
-    for (int i = lane; i < D; i += 32) y[i] = (x[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
-    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+    float s = 0.f, v = 0.f;
+    if (VEC) {
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const int D4 = D >> 2;
+        for (int i = lane; i < D4; i += 32) { const float4 t = x4[i]; s += (t.x + t.y) + (t.z + t.w); }
+        const float mu = warp_sum(s) / (float)D;
+        for (int i = lane; i < D4; i += 32) {
+            const float4 t = x4[i];
+            const float a = t.x - mu, b = t.y - mu, c = t.z - mu, d = t.w - mu;
+            v += (a * a + b * b) + (c * c + d * d);
+        }
+        const float rs = rsqrtf(warp_sum(v) / (float)D + kLnEps);
+        const float4* g4 = reinterpret_cast<const float4*>(gamma);
+        const float4* b4 = reinterpret_cast<const float4*>(beta);
+        float4* y4 = reinterpret_cast<float4*>(y);
+        for (int i = lane; i < D4; i += 32) {
+            const float4 t = x4[i], g = __ldg(g4 + i), bb = __ldg(b4 + i);
+            y4[i] = make_float4((t.x - mu) * rs * g.x + bb.x, (t.y - mu) * rs * g.y + bb.y, (t.z - mu) * rs * g.z + bb.z,
+                                (t.w - mu) * rs * g.w + bb.w);
+        }
+        if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+    } else {
+        for (int i = lane; i < D; i += 32) s += x[i];
+        const float mu = warp_sum(s) / (float)D;
+        for (int i = lane; i < D; i += 32) { const float d = x[i] - mu; v = fmaf(d, d, v); }
+        const float rs = rsqrtf(warp_sum(v) / (float)D + kLnEps);
+        for (int i = lane; i < D; i += 32) y[i] = (x[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
+        if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+    }
 }
 
+template <bool VEC>
 __global__ void __launch_bounds__(256) layernorm_bwd_dx_kernel(int64_t M, int D, const float* __restrict__ dY, int64_t lddy,
                                                                const float* __restrict__ X, int64_t ldx,
                                                                const float* __restrict__ gamma, const float* __restrict__ mean,
@@ -40,21 +64,168 @@ __global__ void __launch_bounds__(256) layernorm_bwd_dx_kernel(int64_t M, int D,
     if (row >= M) return;
     const float* x = X + row * ldx;
     const float* dy = dY + row * lddy;
+    float* dx = dX + row * lddx;
     const float mu = mean[row], rs = rstd[row];
     float s1 = 0.f, s2 = 0.f;
-    for (int i = lane; i < D; i += 32) {
-        const float g = dy[i] * __ldg(gamma + i);
-        s1 += g;
-        s2 = fmaf(g, (x[i] - mu) * rs, s2);
-    }
-    s1 = warp_sum(s1) / (float)D;
-    s2 = warp_sum(s2) / (float)D;
-    float* dx = dX + row * lddx;
-    for (int i = lane; i < D; i += 32) {
-        const float g = dy[i] * __ldg(gamma + i);
-        dx[i] = rs * (g - s1 - (x[i] - mu) * rs * s2);
+    if (VEC) {
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        const float4* d4 = reinterpret_cast<const float4*>(dy);
+        const float4* g4 = reinterpret_cast<const float4*>(gamma);
+        const int D4 = D >> 2;
+        for (int i = lane; i < D4; i += 32) {
+            const float4 t = x4[i], d = d4[i], g = __ldg(g4 + i);
+            const float a = d.x * g.x, b = d.y * g.y, c = d.z * g.z, e = d.w * g.w;
+            s1 += (a + b) + (c + e);
+            s2 += (a * ((t.x - mu) * rs) + b * ((t.y - mu) * rs)) + (c * ((t.z - mu) * rs) + e * ((t.w - mu) * rs));
+        }
+        s1 = warp_sum(s1) / (float)D;
+        s2 = warp_sum(s2) / (float)D;
+        float4* o4 = reinterpret_cast<float4*>(dx);
+        for (int i = lane; i < D4; i += 32) {
+            const float4 t = x4[i], d = d4[i], g = __ldg(g4 + i);
+            o4[i] = make_float4(rs * (d.x * g.x - s1 - (t.x - mu) * rs * s2), rs * (d.y * g.y - s1 - (t.y - mu) * rs * s2),
+                                rs * (d.z * g.z - s1 - (t.z - mu) * rs * s2), rs * (d.w * g.w - s1 - (t.w - mu) * rs * s2));
+        }
+    } else {
+        for (int i = lane; i < D; i += 32) {
+            const float g = dy[i] * __ldg(gamma + i);
+            s1 += g;
+            s2 = fmaf(g, (x[i] - mu) * rs, s2);
+        }
+        s1 = warp_sum(s1) / (float)D;
+        s2 = warp_sum(s2) / (float)D;
+        for (int i = lane; i < D; i += 32) {
+            const float g = dy[i] * __ldg(gamma + i);
+            dx[i] = rs * (g - s1 - (x[i] - mu) * rs * s2);
+        }
     }
 }
+
+// ------------------------------------------------------------------------------------ column reductions ------
+// Vectorised two-stage column reduction (fixed order, no atomics).  A CTA covers 128 columns (one float4 per lane)
+// and a chunk of rows (8 warps interleaved over the rows); stage 2 adds the per-chunk partials.
+//   MODE 0: out0 = sum_rows X                                   (bias gradient of a layer without activation)
+//   MODE 1: out0 = sum_rows dY * xhat, out1 = sum_rows dY       (LayerNorm affine gradients)
+//   MODE 2: dZ = dY * keepmask/(1-p) * act'(.), out0 = sum_rows dZ   (epilogue backward fused with the bias gradient)
+struct ColArgs {
+    int64_t M, N;
+    const float* X; int64_t ldx;         // MODE 0: X, MODE 1/2: dY
+    const float* X2; int64_t ldx2;       // MODE 1: layer input X, MODE 2: forward output Y
+    const float* mean; const float* rstd;
+    const float* res1; int64_t ldr1; const float* res2; int64_t ldr2;
+    int act; float drop_p; uint64_t seed; const uint64_t* seed_dev;
+    float* dZ; int64_t lddz;
+    float* part0; float* part1;
+    int rows_per_chunk;
+};
+
+__device__ __forceinline__ float4 ld4(const float* p, int nvalid) {
+    if (nvalid == 4) return *reinterpret_cast<const float4*>(p);
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (nvalid > 0) r.x = p[0];
+    if (nvalid > 1) r.y = p[1];
+    if (nvalid > 2) r.z = p[2];
+    return r;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) colreduce_vec_kernel(ColArgs a) {
+    __shared__ float4 sh0[8][32];
+    __shared__ float4 sh1[8][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t col = (int64_t)blockIdx.x * 128 + lane * 4;
+    const int nvalid = (int)max((int64_t)0, min((int64_t)4, a.N - col));
+    const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_chunk;
+    const int64_t r1 = min(a.M, r0 + a.rows_per_chunk);
+    float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float keep_scale = 1.0f / (1.0f - a.drop_p);
+    const uint64_t seed = (MODE == 2 && a.drop_p > 0.f) ? a.seed + (a.seed_dev ? *a.seed_dev : 0ull) : 0ull;
+    if (nvalid > 0) {
+        for (int64_t r = r0 + w; r < r1; r += 8) {
+            float4 v = ld4(a.X + r * a.ldx + col, nvalid);
+            if (MODE == 0) {
+                s0.x += v.x; s0.y += v.y; s0.z += v.z; s0.w += v.w;
+            } else if (MODE == 1) {
+                const float4 x = ld4(a.X2 + r * a.ldx2 + col, nvalid);
+                const float mu = a.mean[r], rs = a.rstd[r];
+                s0.x = fmaf(v.x, (x.x - mu) * rs, s0.x); s0.y = fmaf(v.y, (x.y - mu) * rs, s0.y);
+                s0.z = fmaf(v.z, (x.z - mu) * rs, s0.z); s0.w = fmaf(v.w, (x.w - mu) * rs, s0.w);
+                s1.x += v.x; s1.y += v.y; s1.z += v.z; s1.w += v.w;
+            } else {
+                float g[4] = {v.x, v.y, v.z, v.w};
+                bool keep[4] = {true, true, true, true};
+                if (a.drop_p > 0.f) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        keep[j] = hash_uniform(seed, (uint64_t)(r * a.N + col + j)) >= a.drop_p;
+                        g[j] = keep[j] ? g[j] * keep_scale : 0.f;
+                    }
+                }
+                if (a.act == 1) {
+                    const float4 y = ld4(a.X2 + r * a.ldx2 + col, nvalid);
+                    float o[4] = {y.x, y.y, y.z, y.w};
+                    if (a.res1) { const float4 q = ld4(a.res1 + r * a.ldr1 + col, nvalid); o[0] -= q.x; o[1] -= q.y; o[2] -= q.z; o[3] -= q.w; }
+                    if (a.res2) { const float4 q = ld4(a.res2 + r * a.ldr2 + col, nvalid); o[0] -= q.x; o[1] -= q.y; o[2] -= q.z; o[3] -= q.w; }
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        if (keep[j]) {
+                            float av = o[j];
+                            if (a.drop_p > 0.f) av *= (1.0f - a.drop_p);
+                            g[j] *= (av > 0.f) ? 1.0f : (av + 1.0f);
+                        }
+                    }
+                }
+                float* dz = a.dZ + r * a.lddz + col;
+                if (nvalid == 4) *reinterpret_cast<float4*>(dz) = make_float4(g[0], g[1], g[2], g[3]);
+                else { if (nvalid > 0) dz[0] = g[0]; if (nvalid > 1) dz[1] = g[1]; if (nvalid > 2) dz[2] = g[2]; }
+                s0.x += g[0]; s0.y += g[1]; s0.z += g[2]; s0.w += g[3];
+            }
+        }
+    }
+    if (a.part0 == nullptr) return;
+    sh0[w][lane] = s0;
+    if (MODE == 1) sh1[w][lane] = s1;
+    __syncthreads();
+    if (w == 0 && nvalid > 0) {
+        float4 t0 = sh0[0][lane], t1 = sh1[0][lane];
+#pragma unroll
+        for (int j = 1; j < 8; ++j) {
+            const float4 u = sh0[j][lane];
+            t0.x += u.x; t0.y += u.y; t0.z += u.z; t0.w += u.w;
+            if (MODE == 1) { const float4 q = sh1[j][lane]; t1.x += q.x; t1.y += q.y; t1.z += q.z; t1.w += q.w; }
+        }
+        float* p0 = a.part0 + (int64_t)blockIdx.y * a.N + col;
+        const float o0[4] = {t0.x, t0.y, t0.z, t0.w};
+        for (int j = 0; j < nvalid; ++j) p0[j] = o0[j];
+        if (MODE == 1) {
+            float* p1 = a.part1 + (int64_t)blockIdx.y * a.N + col;
+            const float o1[4] = {t1.x, t1.y, t1.z, t1.w};
+            for (int j = 0; j < nvalid; ++j) p1[j] = o1[j];
+        }
+    }
+}
+
+// stage 2: out_k[col] = sum_chunks part_k[chunk][col]; blockIdx.y selects k
+__global__ void colreduce_stage2_vec_kernel(int64_t R, int64_t N, const float* __restrict__ part0, const float* __restrict__ part1,
+                                            float* __restrict__ out0, float* __restrict__ out1) {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= N) return;
+    const float* part = blockIdx.y == 0 ? part0 : part1;
+    float* out = blockIdx.y == 0 ? out0 : out1;
+    float s = 0.f;
+    for (int64_t r = 0; r < R; ++r) s += part[r * N + col];
+    out[col] = s;
+}
+
+// rows per chunk so that the stage-1 grid is about two waves of 148 SMs; multiple of 8 (the warps interleave rows)
+static inline int col_rows_per_chunk(int64_t M, int64_t N) {
+    const int64_t col_blocks = ceil_div(N, 128);
+    int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(ceil_div(296, col_blocks), ceil_div(M, 32)));
+    int64_t rpc = ceil_div(ceil_div(std::max<int64_t>(M, 1), chunks), 8) * 8;
+    return (int)rpc;
+}
+static inline int64_t col_chunks(int64_t M, int64_t N) { return ceil_div(std::max<int64_t>(M, 1), col_rows_per_chunk(M, N)); }
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // Column reductions, stage 1: CTA (32 columns x 8 row-lanes) reduces a chunk of kRowsPerChunk rows.
 constexpr int kRowsPerChunk = 256;
@@ -94,14 +265,6 @@ __global__ void __launch_bounds__(256) colreduce_stage1_kernel(int64_t M, int64_
         part0[(int64_t)blockIdx.y * N + col] = s0;
         if (MODE == 1) part1[(int64_t)blockIdx.y * N + col] = s1;
     }
-}
-
-__global__ void colreduce_stage2_kernel(int64_t R, int64_t N, const float* __restrict__ part, float* __restrict__ out) {
-    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= N) return;
-    float s = 0.f;
-    for (int64_t r = 0; r < R; ++r) s += part[r * N + col];
-    out[col] = s;
 }
 
 // ------------------------------------------------------------------------------------- epilogue backward ------
@@ -222,12 +385,17 @@ extern "C" int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_
     GRAPPA_CHECK_ARG(M >= 0 && D > 0 && D <= (1 << 20), "bad sizes");
     if (M == 0) return 0;
     GRAPPA_CHECK_ARG(X && gamma && beta && Y && mean && rstd, "null pointer");
-    layernorm_fwd_kernel<<<(unsigned)ceil_div(M * 32, 256), 256, 0, (cudaStream_t)stream>>>(M, (int)D, X, ldx, gamma, beta, Y, ldy, mean, rstd);
+    const bool vec = D % 4 == 0 && ldx % 4 == 0 && ldy % 4 == 0 && al16(X) && al16(Y) && al16(gamma) && al16(beta);
+    const unsigned grid = (unsigned)ceil_div(M * 32, 256);
+    if (vec) layernorm_fwd_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(M, (int)D, X, ldx, gamma, beta, Y, ldy, mean, rstd);
+    else layernorm_fwd_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(M, (int)D, X, ldx, gamma, beta, Y, ldy, mean, rstd);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }
 
-extern "C" int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D) { return 2 * ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk) * D; }
+extern "C" int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D) {
+    return 2 * std::max(col_chunks(M, D), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * D;
+}
 
 extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64_t lddy, const float* X, int64_t ldx,
                                     const float* gamma, const float* mean, const float* rstd,
@@ -235,51 +403,98 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
     GRAPPA_CHECK_ARG(M >= 0 && D > 0, "bad sizes");
     GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && dX, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = D % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0 && al16(X) && al16(dY) && al16(dX) && al16(gamma);
     if (M > 0) {
-        layernorm_bwd_dx_kernel<<<(unsigned)ceil_div(M * 32, 256), 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
+        const unsigned grid = (unsigned)ceil_div(M * 32, 256);
+        if (vec) layernorm_bwd_dx_kernel<true><<<grid, 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
+        else layernorm_bwd_dx_kernel<false><<<grid, 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
         GRAPPA_CHECK_LAUNCH();
     }
     if (dgamma || dbeta) {
         GRAPPA_CHECK_ARG(dgamma && dbeta && scratch, "dgamma, dbeta and scratch must be given together");
-        const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
-        float* p0 = scratch;
-        float* p1 = scratch + R * D;
-        dim3 grid((unsigned)ceil_div(D, 32), (unsigned)R);
-        colreduce_stage1_kernel<1><<<grid, 256, 0, st>>>(M, D, dY, lddy, X, ldx, mean, rstd, p0, p1);
-        GRAPPA_CHECK_LAUNCH();
-        colreduce_stage2_kernel<<<(unsigned)ceil_div(D, 128), 128, 0, st>>>(R, D, p0, dgamma);
-        GRAPPA_CHECK_LAUNCH();
-        colreduce_stage2_kernel<<<(unsigned)ceil_div(D, 128), 128, 0, st>>>(R, D, p1, dbeta);
-        GRAPPA_CHECK_LAUNCH();
+        if (vec) {
+            const int64_t R = col_chunks(M, D);
+            ColArgs a = {};
+            a.M = M; a.N = D; a.X = dY; a.ldx = lddy; a.X2 = X; a.ldx2 = ldx; a.mean = mean; a.rstd = rstd;
+            a.part0 = scratch; a.part1 = scratch + R * D; a.rows_per_chunk = col_rows_per_chunk(M, D);
+            dim3 grid((unsigned)ceil_div(D, 128), (unsigned)R);
+            colreduce_vec_kernel<1><<<grid, 256, 0, st>>>(a);
+            GRAPPA_CHECK_LAUNCH();
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 128), 2), 128, 0, st>>>(R, D, a.part0, a.part1, dgamma, dbeta);
+            GRAPPA_CHECK_LAUNCH();
+        } else {
+            const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
+            float* p0 = scratch;
+            float* p1 = scratch + R * D;
+            dim3 grid((unsigned)ceil_div(D, 32), (unsigned)R);
+            colreduce_stage1_kernel<1><<<grid, 256, 0, st>>>(M, D, dY, lddy, X, ldx, mean, rstd, p0, p1);
+            GRAPPA_CHECK_LAUNCH();
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 128), 2), 128, 0, st>>>(R, D, p0, p1, dgamma, dbeta);
+            GRAPPA_CHECK_LAUNCH();
+        }
     }
     return 0;
 }
 
-extern "C" int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N) { return ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk) * N; }
+extern "C" int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N) {
+    return std::max(col_chunks(M, N), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * N;
+}
 
 extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && N > 0, "bad sizes");
     GRAPPA_CHECK_ARG(X && out && scratch, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
+    if (ldx % 4 == 0 && al16(X)) {
+        const int64_t R = col_chunks(M, N);
+        GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
+        ColArgs a = {};
+        a.M = M; a.N = N; a.X = X; a.ldx = ldx; a.part0 = scratch; a.rows_per_chunk = col_rows_per_chunk(M, N);
+        colreduce_vec_kernel<0><<<dim3((unsigned)ceil_div(N, 128), (unsigned)R), 256, 0, st>>>(a);
+        GRAPPA_CHECK_LAUNCH();
+        colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
+        GRAPPA_CHECK_LAUNCH();
+        return 0;
+    }
     const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
     GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
     dim3 grid((unsigned)ceil_div(N, 32), (unsigned)R);
     colreduce_stage1_kernel<0><<<grid, 256, 0, st>>>(M, N, X, ldx, nullptr, 0, nullptr, nullptr, scratch, nullptr);
     GRAPPA_CHECK_LAUNCH();
-    colreduce_stage2_kernel<<<(unsigned)ceil_div(N, 128), 128, 0, st>>>(R, N, scratch, out);
+    colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }
 
 extern "C" int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,
                                    const float* res1, int64_t ldr1, const float* res2, int64_t ldr2, int act,
-                                   float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz, void* stream) {
+                                   float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz,
+                                   float* colsum_out, float* scratch, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && N >= 0, "bad sizes");
     GRAPPA_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "drop_p must be in [0,1)");
+    GRAPPA_CHECK_ARG(colsum_out == nullptr || scratch != nullptr, "column sums need scratch (grappa_colsum_scratch_floats)");
     if (M * N == 0) return 0;
     GRAPPA_CHECK_ARG(dY && dZ && (act == 0 || Y), "null pointer");
-    epilogue_bwd_kernel<<<grid_for(M * N), 256, 0, (cudaStream_t)stream>>>(M, N, dY, lddy, Y, ldy, res1, ldr1, res2, ldr2, act, drop_p, seed, seed_dev, dZ, lddz);
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = lddy % 4 == 0 && lddz % 4 == 0 && al16(dY) && al16(dZ) && (act == 0 || (ldy % 4 == 0 && al16(Y))) &&
+                     (!res1 || (ldr1 % 4 == 0 && al16(res1))) && (!res2 || (ldr2 % 4 == 0 && al16(res2)));
+    if (vec) {
+        const int64_t R = col_chunks(M, N);
+        GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
+        ColArgs a = {};
+        a.M = M; a.N = N; a.X = dY; a.ldx = lddy; a.X2 = Y; a.ldx2 = ldy; a.res1 = res1; a.ldr1 = ldr1; a.res2 = res2; a.ldr2 = ldr2;
+        a.act = act; a.drop_p = drop_p; a.seed = seed; a.seed_dev = seed_dev; a.dZ = dZ; a.lddz = lddz;
+        a.part0 = colsum_out ? scratch : nullptr; a.rows_per_chunk = col_rows_per_chunk(M, N);
+        colreduce_vec_kernel<2><<<dim3((unsigned)ceil_div(N, 128), (unsigned)R), 256, 0, st>>>(a);
+        GRAPPA_CHECK_LAUNCH();
+        if (colsum_out) {
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, colsum_out, nullptr);
+            GRAPPA_CHECK_LAUNCH();
+        }
+        return 0;
+    }
+    epilogue_bwd_kernel<<<grid_for(M * N), 256, 0, st>>>(M, N, dY, lddy, Y, ldy, res1, ldr1, res2, ldr2, act, drop_p, seed, seed_dev, dZ, lddz);
     GRAPPA_CHECK_LAUNCH();
+    if (colsum_out) return grappa_colsum(M, N, dZ, lddz, colsum_out, scratch, stream);
     return 0;
 }
 

@@ -125,31 +125,38 @@ class LinearFn(torch.autograd.Function):
         dy, lddy = _rows2d(dy, "grad")
         M, K = x.shape
         lda = x.stride(0) if M > 1 else K
+        sink = GRAD_SINK
+        want_db = has_bias and ctx.needs_input_grad[2]
+        db = None
+        db_done = False
+        if want_db:
+            tgt = sink.get(ctx.sink_ids[1]) if sink is not None else None
+            db = tgt if tgt is not None else torch.empty((N,), device=dy.device, dtype=torch.float32)
+            scratch = torch.empty((int(L.grappa_colsum_scratch_floats(M, N)),), device=dy.device, dtype=torch.float32)
         if act != ACT_NONE or drop_p > 0:
-            dz = torch.empty((M, N), device=dy.device, dtype=torch.float32)
+            lddz = (N + 3) // 4 * 4
+            dz = torch.empty((M, lddz), device=dy.device, dtype=torch.float32)
             _lib.check(L.grappa_epilogue_bwd(M, N, _p(dy), lddy, _p(y), ldc, _p(r1), r1.stride(0) if r1 is not None and M > 1 else ldc,
                                              _p(r2), r2.stride(0) if r2 is not None and M > 1 else ldc, act, drop_p, seed,
-                                             _p(seed_dev), _p(dz), N, _stream()))
-            lddz = N
+                                             _p(seed_dev), _p(dz), lddz, _p(db) if want_db else None,
+                                             _p(scratch) if want_db else None, _stream()))
+            db_done = want_db
         else:
             dz, lddz = dy, lddy
-        dx = dw = db = None
+        dx = dw = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
             gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
-        sink = GRAD_SINK
         if ctx.needs_input_grad[1]:
             tgt = sink.get(ctx.sink_ids[0]) if sink is not None else None
             dw = tgt if tgt is not None else torch.empty((N, K), device=dy.device, dtype=torch.float32)
             gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
             if tgt is not None:
                 dw = None
-        if has_bias and ctx.needs_input_grad[2]:
-            tgt = sink.get(ctx.sink_ids[1]) if sink is not None else None
-            db = tgt if tgt is not None else torch.empty((N,), device=dy.device, dtype=torch.float32)
-            scratch = torch.empty((int(L.grappa_colsum_scratch_floats(M, N)),), device=dy.device, dtype=torch.float32)
-            _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
-            if tgt is not None:
+        if want_db:
+            if not db_done:
+                _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
+            if sink is not None and sink.get(ctx.sink_ids[1]) is not None:
                 db = None
         dr = dy if ldc == N else dy[:, :N]
         return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,

@@ -50,10 +50,13 @@ int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
                 float* workspace, int64_t workspace_floats, void* stream);
 
 /* dZ = dY * keepmask/(1-p) * act'(.) where the activation output is recovered as (Y - res1 - res2)*(1-p).
- * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL. */
+ * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL.
+ * colsum_out (N, may be NULL): also returns sum_m dZ[m,:] (the bias gradient) from the same pass; needs scratch of
+ * grappa_colsum_scratch_floats(M,N) floats. */
 int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,
                         const float* res1, int64_t ldr1, const float* res2, int64_t ldr2, int act,
-                        float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz, void* stream);
+                        float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dZ, int64_t lddz,
+                        float* colsum_out, float* scratch, void* stream);
 
 /* out[n] = sum_m X[m,n]  (bias gradients).  scratch: at least grappa_colsum_scratch_floats(M,N) floats. */
 int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N);
