@@ -23,6 +23,7 @@ PROTOTYPES = {
     "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P, P, P]),
     "grappa_colsum_scratch_floats": (I64, [I64, I64]),
     "grappa_colsum": (I, [I64, I64, P, I64, P, P, P]),
+    "grappa_colsum_noalloc": (I, [I64, I64, P, I64, P, P]),
     "grappa_layernorm_fwd": (I, [I64, I64, P, I64, P, P, P, I64, P, P, P]),
     "grappa_layernorm_bwd_scratch_floats": (I64, [I64, I64]),
     "grappa_layernorm_bwd": (I, [I64, I64, P, I64, P, I64, P, P, P, P, I64, P, P, P, P]),

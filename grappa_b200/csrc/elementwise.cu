@@ -3,6 +3,7 @@
 // All of these are HBM-bound streaming kernels: coalesced row-major access, one pass over the data where possible,
 // two-stage fixed-order reductions instead of atomics.
 #include "common.cuh"
+#include <mutex>
 
 namespace grappa {
 
@@ -463,6 +464,50 @@ extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, 
     colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
     GRAPPA_CHECK_LAUNCH();
     return 0;
+}
+
+// ---------------------------------------------------------------------------------- allocation-free column sum ---
+// Scratch for grappa_colsum_noalloc.  It lives in the library image: every GPU that loads libgrappa_b200.so carries
+// these 256 KiB until the process exits.  Host code may only use this name to look the array up (cudaGetSymbolAddress);
+// the device address that kernels need is fetched once per device below.
+constexpr int64_t kNoAllocScratchFloats = 64 * 1024;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+
+static std::mutex g_noalloc_mutex;
+static float* g_noalloc_ptr[64] = {nullptr};
+
+// Device address of the static scratch on the CURRENT device; resolved on the first call per device.
+static int noalloc_scratch(float** out) {
+    int dev = -1;
+    GRAPPA_CUDA(cudaGetDevice(&dev));
+    GRAPPA_CHECK_ARG(dev >= 0 && dev < 64, "device ordinal out of range");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        float* ptr = nullptr;
+        GRAPPA_CUDA(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+extern "C" int grappa_colsum_noalloc(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && N > 0, "bad sizes");
+    GRAPPA_CHECK_ARG(X && out, "null pointer");
+    // exactly what grappa_colsum will touch: the float4 path (aligned input) uses far fewer row chunks than the fallback
+    const bool vec = ldx % 4 == 0 && al16(X);
+    const int64_t need = (vec ? col_chunks(M, N) : ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * N;
+    if (need > kNoAllocScratchFloats) {
+        snprintf(g_err, sizeof(g_err),
+                 "grappa_colsum_noalloc: a %lld x %lld column sum needs %lld floats of scratch but the built-in array holds %lld; "
+                 "use grappa_colsum with caller-provided scratch", (long long)M, (long long)N, (long long)need,
+                 (long long)kNoAllocScratchFloats);
+        return 2;
+    }
+    float* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    // Nothing has to be cleared: stage 1 writes every partial that stage 2 reads, so leftovers of earlier calls are dead.
+    return grappa_colsum(M, N, X, ldx, out, scratch, stream);
 }
 
 extern "C" int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,

@@ -62,6 +62,24 @@ int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, con
 int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N);
 int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch, void* stream);
 
+/* Column sum without any allocation on either side of the call (no counterpart in the reference: the reference never
+ * manages scratch itself, PyTorch's caching allocator does).
+ * Same result as grappa_colsum, but the partial-sum scratch is a 256 KiB array built into the library image instead
+ * of a caller buffer.  Meant for callers that were handed device pointers by somebody else and cannot obtain device
+ * memory themselves: a force-field plugin running inside an MD engine's time-step loop (the engine owns a fixed
+ * memory budget and cudaMalloc would stall every stream of the device), or an FFI host (ctypes, cgo, JNI) that has
+ * no device allocator at hand.  The library calls no cudaMalloc / cudaFree / allocating routine here.
+ *   - limit: the partial sums must fit 65536 floats.  For a 16-byte aligned X with ldx % 4 == 0 the need is
+ *     min(ceil(296 / ceil(N/128)), ceil(M/32)) * N floats, i.e. below 40 k for every layer width of the default model
+ *     at any batch size; for unaligned input it is ceil(M/256) * N.  Larger problems are rejected with an error
+ *     message; use grappa_colsum with your own scratch then.
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress, with that device
+ *     current); make that first call before starting any stream capture on the device.
+ *   - all calls on a device share the one array and leave their partial sums in it: two calls that overlap on the
+ *     GPU (different streams, or concurrent host threads) race.  Calls on one stream are safe.  Nothing needs to be
+ *     zeroed between calls. */
+int grappa_colsum_noalloc(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, void* stream);
+
 /* LayerNorm over the last dimension (eps 1e-5).  Replaces torch.nn.LayerNorm at graph_attention.py:293,312,
  * network_utils.py:46,115,129, perm_equiv_transformer.py:80.  mean/rstd: (M) saved for backward. */
 int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_t ldx, const float* gamma, const float* beta,
