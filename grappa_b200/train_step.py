@@ -19,6 +19,7 @@ import torch
 
 from . import _lib, ops
 from .batching import DeviceBatch, PackedBatch
+from .dp import all_reduce_sum_
 from .energy import Energy
 from .plan import get_plan
 
@@ -123,15 +124,14 @@ class TrainStep:
         return st["loss"]
 
     def all_reduce_gradients(self):
-        if self.world_size > 1:
-            torch.distributed.all_reduce(self.flat.grads, op=torch.distributed.ReduceOp.SUM, group=self.pg)
+        self._grad_scale = all_reduce_sum_(self.flat.grads, self.world_size, self.pg)
 
     def optimizer_step(self):
         self.t += 1
         f = self.flat
         _lib.check(_lib.lib().grappa_adamw(f.numel, ops._p(f.params), ops._p(f.grads), ops._p(f.exp_avg), ops._p(f.exp_avg_sq),
                                            self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
-                                           1.0 / self.world_size, ops._stream()))
+                                           getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
 
     def step(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
         loss = self.compute_gradients(packed, load=load)
