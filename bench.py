@@ -172,6 +172,8 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL writes its version banner / debug log to stdout by default; stdout must carry exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         torch.distributed.init_process_group("nccl", device_id=dev)
     if args.math_mode is not None:
         ops.MATH_MODE = args.math_mode

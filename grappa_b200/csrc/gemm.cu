@@ -72,7 +72,7 @@ struct TileLoader {
 };
 
 template <int BM, int BN, int BK, int TM, int TN, bool A_KC, bool B_KC>
-__global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p) {
+__global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p, int64_t k_per_split, float* __restrict__ partial) {
     constexpr int TX = BN / TN, TY = BM / TM;
     static_assert(TX * TY == 256, "256 threads per CTA");
     constexpr int HM = TM / 4, HN = TN / 4;        // number of 4-wide strips per thread
@@ -92,9 +92,12 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p) {
 #pragma unroll
         for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
 
-    const int64_t nk = (p.K + BK - 1) / BK;
-    la.load(p.A, p.lda, m0, p.M, 0, p.K, p.a_vec, tid);
-    lb.load(p.B, p.ldb, n0, p.N, 0, p.K, p.b_vec, tid);
+    // split-K: blockIdx.z owns k in [kbeg, kend); partial tiles are written raw to `partial`
+    const int64_t kbeg = (int64_t)blockIdx.z * k_per_split;
+    const int64_t kend = min(p.K, kbeg + k_per_split);
+    const int64_t nk = (kend - kbeg + BK - 1) / BK;
+    la.load(p.A, p.lda, m0, p.M, kbeg, kend, p.a_vec, tid);
+    lb.load(p.B, p.ldb, n0, p.N, kbeg, kend, p.b_vec, tid);
     la.template store<LDA>(As[0], tid);
     lb.template store<LDB>(Bs[0], tid);
     __syncthreads();
@@ -102,8 +105,8 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p) {
     for (int64_t kt = 0; kt < nk; ++kt) {
         const int cur = kt & 1;
         if (kt + 1 < nk) {
-            la.load(p.A, p.lda, m0, p.M, (kt + 1) * BK, p.K, p.a_vec, tid);
-            lb.load(p.B, p.ldb, n0, p.N, (kt + 1) * BK, p.K, p.b_vec, tid);
+            la.load(p.A, p.lda, m0, p.M, kbeg + (kt + 1) * BK, kend, p.a_vec, tid);
+            lb.load(p.B, p.ldb, n0, p.N, kbeg + (kt + 1) * BK, kend, p.b_vec, tid);
         }
         const float* as = As[cur];
         const float* bs = Bs[cur];
@@ -132,6 +135,20 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p) {
         __syncthreads();
     }
 
+    if (partial != nullptr) {
+        float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
+#pragma unroll
+        for (int i = 0; i < TM; ++i) {
+            const int64_t m = m0 + (i / 4) * (BM / HM) + ty * 4 + (i % 4);
+            if (m >= p.M) continue;
+#pragma unroll
+            for (int j = 0; j < TN; ++j) {
+                const int64_t n = n0 + (j / 4) * (BN / HN) + tx * 4 + (j % 4);
+                if (n < p.N) dst[m * p.N + n] = acc[i][j];
+            }
+        }
+        return;
+    }
     // epilogue
     const bool has_drop = p.drop_p > 0.f;
     const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
@@ -172,12 +189,25 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p) {
 }
 
 template <int BM, int BN, int BK, int TM, int TN>
-static int launch_layout(int layout, const GemmParams& p, cudaStream_t st) {
-    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM));
-    if (layout == 0) sgemm_kernel<BM, BN, BK, TM, TN, true, true><<<grid, 256, 0, st>>>(p);
-    else if (layout == 1) sgemm_kernel<BM, BN, BK, TM, TN, true, false><<<grid, 256, 0, st>>>(p);
-    else sgemm_kernel<BM, BN, BK, TM, TN, false, false><<<grid, 256, 0, st>>>(p);
+static int launch_layout(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats) {
+    const int64_t tiles = ceil_div(p.N, BN) * ceil_div(p.M, BM);
+    // few output tiles and a long reduction (weight gradients of the narrow output layers): split K over CTAs
+    int splits = 1;
+    int64_t kps = p.K;
+    if (workspace != nullptr && tiles <= 37 && p.K >= 512) {
+        const int64_t want = std::min<int64_t>(ceil_div(148, tiles), p.K / 128);
+        if (want > 1 && want * p.M * p.N <= workspace_floats) {
+            kps = ceil_div(ceil_div(p.K, want), BK) * BK;
+            splits = (int)ceil_div(p.K, kps);
+        }
+    }
+    float* partial = splits > 1 ? workspace : nullptr;
+    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM), (unsigned)splits);
+    if (layout == 0) sgemm_kernel<BM, BN, BK, TM, TN, true, true><<<grid, 256, 0, st>>>(p, kps, partial);
+    else if (layout == 1) sgemm_kernel<BM, BN, BK, TM, TN, true, false><<<grid, 256, 0, st>>>(p, kps, partial);
+    else sgemm_kernel<BM, BN, BK, TM, TN, false, false><<<grid, 256, 0, st>>>(p, kps, partial);
     GRAPPA_CHECK_LAUNCH();
+    if (splits > 1) return splitk_reduce(p, splits, workspace, st);
     return 0;
 }
 
@@ -215,6 +245,6 @@ extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
     }
     // pick the large tile only when it still fills the machine (148 SMs) reasonably
     const int64_t big_ctas = ceil_div(M, 128) * ceil_div(N, 128);
-    if (big_ctas >= 120) return launch_layout<128, 128, 16, 8, 8>(layout, p, st);
-    return launch_layout<64, 64, 16, 4, 4>(layout, p, st);
+    if (big_ctas >= 120) return launch_layout<128, 128, 16, 8, 8>(layout, p, st, workspace, workspace_floats);
+    return launch_layout<64, 64, 16, 4, 4>(layout, p, st, workspace, workspace_floats);
 }

@@ -15,4 +15,7 @@ struct GemmParams {
 int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
                      bool* handled);   // gemm_tc.cu
 
+// C = epilogue(sum_z partial[z]) in fixed order; shared by both GEMM paths (gemm_tc.cu)
+int splitk_reduce(const GemmParams& p, int splits, const float* partial, cudaStream_t st);
+
 }  // namespace grappa

@@ -81,7 +81,7 @@ def _workspace(device):
 
 def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
          drop_p=0.0, seed=0, seed_dev=None):
-    ws = _workspace(C.device) if MATH_MODE == 1 else None
+    ws = _workspace(C.device)
     _lib.check(_lib.lib().grappa_gemm(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act,
                                       _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), MATH_MODE,
                                       _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))

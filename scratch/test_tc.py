@@ -40,3 +40,7 @@ for layout in (0, 1, 2):
         ok &= e1 < 3e-6
         print(f"{flag} layout {layout} M{M} N{N} K{K}: tc err/sqrtK {e1:.2e}   ffma {e0:.2e}", flush=True)
 print("ALL OK" if ok else "FAILURES")
+# FFMA split-K (tiny outputs)
+for (l, M, N, K) in [(2, 2, 256, 4352), (2, 6, 256, 6080), (2, 512, 83, 1280), (0, 40, 8, 4096)]:
+    e0 = run(l, M, N, K, 0, bias=True)
+    print(("OK " if e0 < 3e-6 else "BAD"), "ffma split-K", l, M, N, K, f"{e0:.2e}")
