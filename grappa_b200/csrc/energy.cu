@@ -19,6 +19,8 @@ namespace grappa {
 
 // ------------------------------------------------------------------------------------------------ host plan ----
 
+constexpr int kBlkStride = 12;   // ints per block row: a0, na, mol, rec0, n_rec, n_slots, n_blocks_of_mol, j, n_rec per level[4]
+
 struct LevelIdx {
     const int64_t* idx;
     int64_t T;
@@ -95,10 +97,11 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
     GRAPPA_CHECK_ARG(max_slots < (1 << 30), "block too large");
 
     for (int64_t b = 0; b < nB; ++b) {
-        int32_t* o = blk + b * 8;
+        int32_t* o = blk + b * kBlkStride;
         o[0] = blocks[b].a0; o[1] = blocks[b].na; o[2] = blocks[b].mol; o[3] = (int32_t)rec_cnt[b];
         o[4] = (int32_t)(rec_cnt[b + 1] - rec_cnt[b]); o[5] = (int32_t)slot_cnt[b];
         o[6] = blocks[b].nb; o[7] = blocks[b].j;
+        o[8] = o[9] = o[10] = o[11] = 0;      // records per level (filled in pass 2)
     }
     for (int64_t a = 0; a <= n_atoms; ++a) pull_ptr[a] = (int32_t)inc_cnt[a];
 
@@ -118,6 +121,7 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
             for (int q = 0; q < nt; ++q) {
                 const int32_t b = tb[q];
                 const int64_t r = rec_fill[b]++;
+                blk[(int64_t)b * kBlkStride + 8 + l]++;
                 rec_meta[r * 2 + 0] = l | ((b == owner) ? 4 : 0);
                 rec_meta[r * 2 + 1] = (int32_t)t;
                 for (int i = 0; i < 4; ++i) {
@@ -164,6 +168,7 @@ struct EnergyParams {
     float* partial;
     int64_t n_mol, C;
     int term_mask;
+    int max_block_atoms;
 };
 
 __device__ __forceinline__ V3 load3(const float* __restrict__ p) { return v3(__ldg(p), __ldg(p + 1), __ldg(p + 2)); }
@@ -185,110 +190,151 @@ __device__ __forceinline__ void torsion_terms(const float* __restrict__ k, int P
     }
 }
 
-template <int CC>
+// Position of one atom for conformation c (chunk-local).  LOCAL: every atom of every record belongs to this CTA's
+// block (true whenever no molecule spans several blocks), so positions always come from the shared-memory copy.
+template <int CC, bool LOCAL>
+__device__ __forceinline__ V3 atom_pos(const float* __restrict__ xs, const float* __restrict__ xyz, int a, int a0, int na,
+                                       int c, int64_t C, int64_t c0) {
+    const unsigned al = (unsigned)(a - a0);
+    if (LOCAL || al < (unsigned)na) {
+        const float* q = xs + (al * CC + c) * 3;
+        return v3(q[0], q[1], q[2]);
+    }
+    const float* q = xyz + ((int64_t)a * C + c0 + c) * 3;
+    return v3(__ldg(q), __ldg(q + 1), __ldg(q + 2));
+}
+
+__device__ __forceinline__ void put3(float* __restrict__ stage, int slot, int cc, int c, float x, float y, float z) {
+    if (slot >= 0) { float* o = stage + (slot * cc + c) * 3; o[0] = x; o[1] = y; o[2] = z; }
+}
+
+template <int CC, bool LOCAL>
 __global__ void __launch_bounds__(kEnergyThreads) energy_fwd_kernel(EnergyParams p) {
     extern __shared__ float smem[];
-    float* red = smem;                          // [4][kEnergyThreads]
-    float* stage = smem + 4 * kEnergyThreads;   // [slot][CC][3]
+    float* red = smem;                                        // [4][kEnergyThreads]
+    float* xs = smem + 4 * kEnergyThreads;                    // [block atom][CC][3]
+    float* stage = xs + (size_t)p.max_block_atoms * CC * 3;   // [slot][CC][3]
 
     const int b = blockIdx.x;
     const int64_t c0 = (int64_t)blockIdx.y * CC;
-    const int32_t* bi = p.blk + (int64_t)b * 8;
-    const int a0 = bi[0], na = bi[1], mol = bi[2], r0 = bi[3], nr = bi[4], nb = bi[6];
+    const int32_t* bi = p.blk + (int64_t)b * kBlkStride;
+    const int a0 = bi[0], na = bi[1], mol = bi[2], r0 = bi[3], nb = bi[6];
+    const int n_bond = bi[8], n_angle = bi[9], n_proper = bi[10], n_improper = bi[11];
     const int tid = threadIdx.x;
     const int64_t C = p.C;
+    const int nc = (int)min((int64_t)CC, C - c0);             // valid conformations of this chunk
 
-    float eacc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int item = tid; item < nr * CC; item += kEnergyThreads) {
-        const int r = item / CC, c = item % CC;
-        const int64_t conf = c0 + c;
-        if (conf >= C) continue;
-        const int64_t rr = (int64_t)r0 + r;
-        const int2 meta = __ldg(reinterpret_cast<const int2*>(p.rec_meta) + rr);
-        const int level = meta.x & 3;
-        if (!((p.term_mask >> level) & 1)) {
-            // masked term: its slots must still read as zero in phase 2
-            const int4 sl = __ldg(reinterpret_cast<const int4*>(p.rec_slot) + rr);
-            const int s4[4] = {sl.x, sl.y, sl.z, sl.w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (s4[i] >= 0) { float* d = stage + ((int64_t)s4[i] * CC + c) * 3; d[0] = 0.f; d[1] = 0.f; d[2] = 0.f; }
-            continue;
-        }
-        const bool owner = (meta.x & 4) != 0;
-        const int t = meta.y;
-        const int4 at = __ldg(reinterpret_cast<const int4*>(p.rec_atoms) + rr);
-        const int4 sl = __ldg(reinterpret_cast<const int4*>(p.rec_slot) + rr);
-        const float* base = p.xyz + conf * 3;
-        const V3 p0 = load3(base + (int64_t)at.x * C * 3);
-        const V3 p1 = load3(base + (int64_t)at.y * C * 3);
-        V3 g[4];
-        float E, coord;
-        if (level == 0) {
-            float r_; V3 g0;
-            bond_geom(p0, p1, r_, g0);
-            const float k = __ldg(p.k[0] + t), d = r_ - __ldg(p.eq[0] + t);
-            E = 0.5f * k * d * d;
-            const float f = k * d;
-            g[0] = f * g0; g[1] = (-f) * g0;
-            coord = r_;
-        } else if (level == 1) {
-            const V3 p2 = load3(base + (int64_t)at.z * C * 3);
-            float th; V3 g0, g2;
-            angle_geom(p0, p1, p2, th, g0, g2);
-            const float k = __ldg(p.k[1] + t), d = th - __ldg(p.eq[1] + t);
-            E = 0.5f * k * d * d;
-            const float f = k * d;
-            g[0] = f * g0; g[2] = f * g2; g[1] = (-f) * (g0 + g2);
-            coord = th;
-        } else {
-            const V3 p2 = load3(base + (int64_t)at.z * C * 3);
-            const V3 p3 = load3(base + (int64_t)at.w * C * 3);
-            float cphi, sphi; V3 gg[4];
-            dihedral_geom(p0, p1, p2, p3, cphi, sphi, gg);
-            const int P = level == 2 ? p.P4 : p.P4i;
-            float dE;
-            torsion_terms(p.k[level] + (int64_t)t * P, P, cphi, sphi, E, dE);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) g[i] = dE * gg[i];
-            coord = 0.f;
-            if (owner && p.x[level]) coord = atan2f(sphi, cphi);
-        }
-        const int s4[4] = {sl.x, sl.y, sl.z, sl.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (s4[i] >= 0) {
-                float* d = stage + ((int64_t)s4[i] * CC + c) * 3;
-                d[0] = g[i].x; d[1] = g[i].y; d[2] = g[i].z;
-            }
-        }
-        if (owner) {
-            eacc[level] += E;
-            if (p.x[level]) p.x[level][(int64_t)t * C + conf] = coord;
-            if (p.e[level]) p.e[level][(int64_t)t * C + conf] = E;
-        }
+    // phase 0: the block's coordinates for this chunk, one coalesced pass (CC*3 contiguous floats per atom)
+    for (int j = tid; j < na * CC * 3; j += kEnergyThreads) {
+        const int al = j / (CC * 3), rem = j % (CC * 3);
+        xs[j] = (rem < nc * 3) ? __ldg(p.xyz + ((int64_t)(a0 + al) * C + c0) * 3 + rem) : 0.f;
     }
+    __syncthreads();
+
+    // phase 1: one thread per (tuple record, conformation); records are sorted by level inside a block, so each level
+    // gets its own loop (no per-item level dispatch).  Masked levels write zeros into their slots.
+    float e0 = 0.f, e1 = 0.f, e2 = 0.f, e3 = 0.f;
+    const bool on0 = p.term_mask & 1, on1 = p.term_mask & 2, on2 = p.term_mask & 4, on3 = p.term_mask & 8;
+
+    // One flattened item list ordered by cost (torsions, then angles, then bonds): every pass of 256 items is of
+    // (nearly) one kind, and the per-thread work is balanced to within one cheap item before the barrier.
+    const int n_tor = n_proper + n_improper;
+    for (int item = tid; item < (n_tor + n_angle + n_bond) * CC; item += kEnergyThreads) {
+      const int rl_all = item / CC, c = item % CC;
+      if (c >= nc) continue;
+      if (rl_all >= n_tor + n_angle) {                                             // ---- bonds
+        const int r = r0 + (rl_all - n_tor - n_angle);
+        const int2 meta = __ldg(reinterpret_cast<const int2*>(p.rec_meta) + r);
+        const int4 at = __ldg(reinterpret_cast<const int4*>(p.rec_atoms) + r);
+        const int4 sl = __ldg(reinterpret_cast<const int4*>(p.rec_slot) + r);
+        float f = 0.f, E = 0.f, r_ = 0.f; V3 g0 = v3(0.f, 0.f, 0.f);
+        if (on0) {
+            bond_geom(atom_pos<CC, LOCAL>(xs, p.xyz, at.x, a0, na, c, C, c0), atom_pos<CC, LOCAL>(xs, p.xyz, at.y, a0, na, c, C, c0), r_, g0);
+            const float k = __ldg(p.k[0] + meta.y), d = r_ - __ldg(p.eq[0] + meta.y);
+            f = k * d; E = 0.5f * f * d;
+        }
+        put3(stage, sl.x, CC, c, f * g0.x, f * g0.y, f * g0.z);
+        put3(stage, sl.y, CC, c, -f * g0.x, -f * g0.y, -f * g0.z);
+        if (on0 && (meta.x & 4)) {
+            e0 += E;
+            if (p.x[0]) p.x[0][(int64_t)meta.y * C + c0 + c] = r_;
+            if (p.e[0]) p.e[0][(int64_t)meta.y * C + c0 + c] = E;
+        }
+      } else if (rl_all >= n_tor) {                                                // ---- angles
+        const int r = r0 + n_bond + (rl_all - n_tor);
+        const int2 meta = __ldg(reinterpret_cast<const int2*>(p.rec_meta) + r);
+        const int4 at = __ldg(reinterpret_cast<const int4*>(p.rec_atoms) + r);
+        const int4 sl = __ldg(reinterpret_cast<const int4*>(p.rec_slot) + r);
+        float f = 0.f, E = 0.f, th = 0.f; V3 g0 = v3(0.f, 0.f, 0.f), g2 = g0;
+        if (on1) {
+            angle_geom(atom_pos<CC, LOCAL>(xs, p.xyz, at.x, a0, na, c, C, c0), atom_pos<CC, LOCAL>(xs, p.xyz, at.y, a0, na, c, C, c0),
+                       atom_pos<CC, LOCAL>(xs, p.xyz, at.z, a0, na, c, C, c0), th, g0, g2);
+            const float k = __ldg(p.k[1] + meta.y), d = th - __ldg(p.eq[1] + meta.y);
+            f = k * d; E = 0.5f * f * d;
+        }
+        put3(stage, sl.x, CC, c, f * g0.x, f * g0.y, f * g0.z);
+        put3(stage, sl.y, CC, c, -f * (g0.x + g2.x), -f * (g0.y + g2.y), -f * (g0.z + g2.z));
+        put3(stage, sl.z, CC, c, f * g2.x, f * g2.y, f * g2.z);
+        if (on1 && (meta.x & 4)) {
+            e1 += E;
+            if (p.x[1]) p.x[1][(int64_t)meta.y * C + c0 + c] = th;
+            if (p.e[1]) p.e[1][(int64_t)meta.y * C + c0 + c] = E;
+        }
+      } else {                                                                     // ---- proper + improper torsions
+        const int rl = rl_all;
+        const int r = r0 + n_bond + n_angle + rl;
+        const bool improper = rl >= n_proper;
+        const int2 meta = __ldg(reinterpret_cast<const int2*>(p.rec_meta) + r);
+        const int4 at = __ldg(reinterpret_cast<const int4*>(p.rec_atoms) + r);
+        const int4 sl = __ldg(reinterpret_cast<const int4*>(p.rec_slot) + r);
+        float dE = 0.f, E = 0.f, cphi = 1.f, sphi = 0.f;
+        V3 gg[4];
 #pragma unroll
-    for (int l = 0; l < 4; ++l) red[l * kEnergyThreads + tid] = eacc[l];
+        for (int i = 0; i < 4; ++i) gg[i] = v3(0.f, 0.f, 0.f);
+        const bool on = improper ? on3 : on2;
+        if (on) {
+            dihedral_geom(atom_pos<CC, LOCAL>(xs, p.xyz, at.x, a0, na, c, C, c0), atom_pos<CC, LOCAL>(xs, p.xyz, at.y, a0, na, c, C, c0),
+                          atom_pos<CC, LOCAL>(xs, p.xyz, at.z, a0, na, c, C, c0), atom_pos<CC, LOCAL>(xs, p.xyz, at.w, a0, na, c, C, c0),
+                          cphi, sphi, gg);
+            const int P = improper ? p.P4i : p.P4;
+            torsion_terms((improper ? p.k[3] : p.k[2]) + (int64_t)meta.y * P, P, cphi, sphi, E, dE);
+        }
+        put3(stage, sl.x, CC, c, dE * gg[0].x, dE * gg[0].y, dE * gg[0].z);
+        put3(stage, sl.y, CC, c, dE * gg[1].x, dE * gg[1].y, dE * gg[1].z);
+        put3(stage, sl.z, CC, c, dE * gg[2].x, dE * gg[2].y, dE * gg[2].z);
+        put3(stage, sl.w, CC, c, dE * gg[3].x, dE * gg[3].y, dE * gg[3].z);
+        if (on && (meta.x & 4)) {
+            if (improper) e3 += E; else e2 += E;
+            float* xo = improper ? p.x[3] : p.x[2];
+            float* eo = improper ? p.e[3] : p.e[2];
+            if (xo) xo[(int64_t)meta.y * C + c0 + c] = atan2f(sphi, cphi);
+            if (eo) eo[(int64_t)meta.y * C + c0 + c] = E;
+        }
+      }
+    }
+    red[0 * kEnergyThreads + tid] = e0;
+    red[1 * kEnergyThreads + tid] = e1;
+    red[2 * kEnergyThreads + tid] = e2;
+    red[3 * kEnergyThreads + tid] = e3;
     __syncthreads();
 
     // phase 2: pull-reduce the staged gradient vectors per (atom, conformation), fixed order
     for (int j = tid; j < na * CC; j += kEnergyThreads) {
         const int al = j / CC, c = j % CC;
-        const int64_t conf = c0 + c;
-        if (conf >= C) continue;
+        if (c >= nc) continue;
         const int a = a0 + al;
         const int q0 = __ldg(p.pull_ptr + a), q1 = __ldg(p.pull_ptr + a + 1);
         float gx = 0.f, gy = 0.f, gz = 0.f;
         for (int q = q0; q < q1; ++q) {
-            const float* s = stage + ((int64_t)__ldg(p.pull_slot + q) * CC + c) * 3;
-            gx += s[0]; gy += s[1]; gz += s[2];
+            const float* sp = stage + (__ldg(p.pull_slot + q) * CC + c) * 3;
+            gx += sp[0]; gy += sp[1]; gz += sp[2];
         }
-        float* o = p.gradient + ((int64_t)a * C + conf) * 3;
+        float* o = p.gradient + ((int64_t)a * C + c0 + c) * 3;
         o[0] = gx; o[1] = gy; o[2] = gz;
     }
 
     // energies: thread j < 4*CC sums its (term, conformation) column over the CTA in thread order
+    // (item % CC == tid % CC for every item of a thread because kEnergyThreads % CC == 0)
     float tsum = 0.f;
     if (tid < 4 * CC) {
         const int l = tid / CC, c = tid % CC;
@@ -316,7 +362,7 @@ __global__ void energy_finalize_kernel(EnergyParams p, int64_t n_blocks) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_blocks * p.C) return;
     const int64_t b = i / p.C, conf = i % p.C;
-    const int32_t* bi = p.blk + b * 8;
+    const int32_t* bi = p.blk + b * kBlkStride;
     if (bi[6] <= 1 || bi[7] != 0) return;
     const int nb = bi[6], mol = bi[2];
     float tot = 0.f;
@@ -408,18 +454,23 @@ __global__ void __launch_bounds__(256) energy_vjp_kernel(VjpParams p) {
     }
 }
 
-template <int CC>
-static int launch_energy(const EnergyParams& p, int64_t n_blocks, int max_slots, cudaStream_t st) {
-    const size_t smem = (size_t)(4 * kEnergyThreads + (size_t)max_slots * CC * 3) * sizeof(float);
+template <int CC, bool LOCAL>
+static int launch_energy2(const EnergyParams& p, int64_t n_blocks, int max_slots, cudaStream_t st) {
+    const size_t smem = (size_t)(4 * kEnergyThreads + ((size_t)max_slots + p.max_block_atoms) * CC * 3) * sizeof(float);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        GRAPPA_CUDA(cudaFuncSetAttribute(energy_fwd_kernel<CC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GRAPPA_CUDA(cudaFuncSetAttribute(energy_fwd_kernel<CC, LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     dim3 grid((unsigned)n_blocks, (unsigned)ceil_div(p.C, CC));
-    energy_fwd_kernel<CC><<<grid, kEnergyThreads, smem, st>>>(p);
+    energy_fwd_kernel<CC, LOCAL><<<grid, kEnergyThreads, smem, st>>>(p);
     GRAPPA_CHECK_LAUNCH();
     return 0;
+}
+
+template <int CC>
+static int launch_energy(const EnergyParams& p, int64_t n_blocks, int max_slots, bool local, cudaStream_t st) {
+    return local ? launch_energy2<CC, true>(p, n_blocks, max_slots, st) : launch_energy2<CC, false>(p, n_blocks, max_slots, st);
 }
 
 }  // namespace grappa
@@ -429,7 +480,7 @@ static int g_energy_cc_override = -1;
 extern "C" int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, const float* xyz,
                                  int64_t n_blocks, const int32_t* blk, const int32_t* rec_atoms, const int32_t* rec_meta,
                                  const int32_t* rec_slot, const int32_t* pull_ptr, const int32_t* pull_slot,
-                                 int max_slots, int any_multi_block, int term_mask,
+                                 int max_slots, int max_block_atoms, int any_multi_block, int term_mask,
                                  const float* k2, const float* eq2, const float* k3, const float* eq3,
                                  const float* k4, int P4, const float* k4i, int P4i,
                                  float* energy, float* term_energy, float* gradient,
@@ -447,7 +498,7 @@ extern "C" int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, cons
     p.k[0] = k2; p.k[1] = k3; p.k[2] = k4; p.k[3] = k4i; p.eq[0] = eq2; p.eq[1] = eq3;
     p.P4 = P4; p.P4i = P4i; p.energy = energy; p.term_energy = term_energy; p.gradient = gradient;
     p.x[0] = x2; p.x[1] = x3; p.x[2] = x4; p.x[3] = x4i; p.e[0] = e2; p.e[1] = e3; p.e[2] = e4; p.e[3] = e4i;
-    p.partial = partial; p.n_mol = n_mol; p.C = C; p.term_mask = term_mask;
+    p.partial = partial; p.n_mol = n_mol; p.C = C; p.term_mask = term_mask; p.max_block_atoms = max_block_atoms;
     cudaStream_t st = (cudaStream_t)stream;
 
     // conformations per CTA: the staging array holds max_slots * CC float3; keep it near 40 KB so that ~5 CTAs
@@ -458,17 +509,18 @@ extern "C" int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, cons
         g_energy_cc_override = e ? atoi(e) : 0;
     }
     if (g_energy_cc_override > 0) cc = g_energy_cc_override;
-    else while (cc > 1 && ((int64_t)max_slots * cc * 12 > 40 * 1024 || cc / 2 >= C)) cc >>= 1;
-    GRAPPA_CHECK_ARG((int64_t)max_slots * cc * 12 + 4096 <= 200 * 1024, "atom block too large for shared memory; rebuild the plan with fewer block_atoms");
+    else while (cc > 1 && ((int64_t)(max_slots + max_block_atoms) * cc * 12 > 40 * 1024 || cc / 2 >= C)) cc >>= 1;
+    GRAPPA_CHECK_ARG(max_block_atoms > 0, "max_block_atoms must be positive");
+    GRAPPA_CHECK_ARG((int64_t)(max_slots + max_block_atoms) * cc * 12 + 4096 <= 200 * 1024, "atom block too large for shared memory; rebuild the plan with fewer block_atoms");
     GRAPPA_CHECK_ARG(ceil_div(C, cc) <= 65535, "too many conformation chunks");
     int rc;
     switch (cc) {
-        case 32: rc = launch_energy<32>(p, n_blocks, max_slots, st); break;
-        case 16: rc = launch_energy<16>(p, n_blocks, max_slots, st); break;
-        case 8: rc = launch_energy<8>(p, n_blocks, max_slots, st); break;
-        case 4: rc = launch_energy<4>(p, n_blocks, max_slots, st); break;
-        case 2: rc = launch_energy<2>(p, n_blocks, max_slots, st); break;
-        case 1: rc = launch_energy<1>(p, n_blocks, max_slots, st); break;
+        case 32: rc = launch_energy<32>(p, n_blocks, max_slots, !any_multi_block, st); break;
+        case 16: rc = launch_energy<16>(p, n_blocks, max_slots, !any_multi_block, st); break;
+        case 8: rc = launch_energy<8>(p, n_blocks, max_slots, !any_multi_block, st); break;
+        case 4: rc = launch_energy<4>(p, n_blocks, max_slots, !any_multi_block, st); break;
+        case 2: rc = launch_energy<2>(p, n_blocks, max_slots, !any_multi_block, st); break;
+        case 1: rc = launch_energy<1>(p, n_blocks, max_slots, !any_multi_block, st); break;
         default: GRAPPA_CHECK_ARG(false, "GRAPPA_ENERGY_CC must be a power of two <= 32"); rc = 2;
     }
     if (rc) return rc;

@@ -27,11 +27,27 @@ GHD V3 operator*(float s, V3 a) { return v3(s * a.x, s * a.y, s * a.z); }
 GHD float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 GHD V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 
+// Device: single-instruction approximations (MUFU, <= 2 ulp), far inside the rtol 1e-4 budget of the path and free of
+// the IEEE slow paths that the plain operators carry without --use_fast_math.  Host: exact, for unit tests.
 GHD float rsqrt_(float x) {
 #ifdef __CUDA_ARCH__
-    return rsqrtf(x);
+    float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
 #else
     return 1.0f / sqrtf(x);
+#endif
+}
+GHD float rcp_(float x) {
+#ifdef __CUDA_ARCH__
+    float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#else
+    return 1.0f / x;
+#endif
+}
+GHD float sqrt_(float x) {
+#ifdef __CUDA_ARCH__
+    float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#else
+    return sqrtf(x);
 #endif
 }
 
@@ -51,12 +67,12 @@ GHD void angle_geom(V3 p0, V3 p1, V3 p2, float& theta, V3& g0, V3& g2) {
     V3 u = p0 - p1, v = p2 - p1;
     V3 c = cross(u, v);
     float c2 = dot(c, c), uv = dot(u, v);
-    float cn = sqrtf(c2);
+    float icn = c2 > kTiny ? rsqrt_(c2) : 0.f;
+    float cn = c2 * icn;
     theta = atan2f(cn, uv);
     float u2 = dot(u, u), v2 = dot(v, v);
-    float icn = c2 > kTiny ? 1.0f / cn : 0.f;
-    float su = u2 > kTiny ? icn / u2 : 0.f;
-    float sv = v2 > kTiny ? icn / v2 : 0.f;
+    float su = u2 > kTiny ? icn * rcp_(u2) : 0.f;
+    float sv = v2 > kTiny ? icn * rcp_(v2) : 0.f;
     g0 = su * cross(u, c);
     g2 = sv * cross(c, v);
 }
@@ -74,8 +90,8 @@ GHD void dihedral_geom(V3 p0, V3 p1, V3 p2, V3 p3, float& cphi, float& sphi, V3 
     float irho = rho2 > kTiny ? rsqrt_(rho2) : 0.f;
     cphi = rho2 > kTiny ? x * irho : 1.f;
     sphi = y * irho;
-    float iA2 = A2 > kTiny ? 1.0f / A2 : 0.f;
-    float iB2 = B2 > kTiny ? 1.0f / B2 : 0.f;
+    float iA2 = A2 > kTiny ? rcp_(A2) : 0.f;
+    float iB2 = B2 > kTiny ? rcp_(B2) : 0.f;
     // phi_ref = -phi_BK (Blondel & Karplus 1996 sign convention), hence the signs below.
     float fa = Gn * iA2, fb = Gn * iB2;
     float ta = dot(F, G) * iA2 * iG, tb = dot(H, G) * iB2 * iG;

@@ -142,7 +142,7 @@ def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS) -> BatchPlan:
     _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, _np_ptr(sizes),
                                           None, None, None, None, None, None, None))
     nB, nR, nP = int(sizes[0]), int(sizes[1]), int(sizes[2])
-    blk = np.zeros(nB * 8, np.int32)
+    blk = np.zeros(nB * 12, np.int32)
     rec_atoms = np.zeros(nR * 4, np.int32)
     rec_meta = np.zeros(nR * 2, np.int32)
     rec_slot = np.zeros(nR * 4, np.int32)

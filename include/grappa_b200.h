@@ -170,7 +170,7 @@ int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_
                              const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
                              const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
                              int block_atoms, int64_t* sizes_out,
-                             int32_t* blk /*(n_blocks,8)*/, int32_t* rec_atoms /*(n_records,4)*/,
+                             int32_t* blk /*(n_blocks,12)*/, int32_t* rec_atoms /*(n_records,4)*/,
                              int32_t* rec_meta /*(n_records,2)*/, int32_t* rec_slot /*(n_records,4)*/,
                              int32_t* pull_ptr /*(n_atoms+1)*/, int32_t* pull_slot /*(n_pull)*/,
                              int32_t* tuple_mol /*(T2+T3+T4+T4i)*/);
@@ -184,7 +184,7 @@ int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_
 int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, const float* xyz,
                       int64_t n_blocks, const int32_t* blk, const int32_t* rec_atoms, const int32_t* rec_meta,
                       const int32_t* rec_slot, const int32_t* pull_ptr, const int32_t* pull_slot,
-                      int max_slots, int any_multi_block, int term_mask,
+                      int max_slots, int max_block_atoms, int any_multi_block, int term_mask,
                       const float* k2, const float* eq2, const float* k3, const float* eq3,
                       const float* k4, int P4, const float* k4i, int P4i,
                       float* energy, float* term_energy, float* gradient,

@@ -186,3 +186,44 @@ def test_api_errors_and_edge_cases():
     assert out.nodes["n4"].data["k"].shape == (0, 3)
     with pytest.raises(Exception):
         model(S.cfg1_graph(n_confs=1))          # CPU graph: no fallback
+
+
+def test_cfg3_inference_matches_oracle_at_scale():
+    """BASELINE cfg 3 shape (scaled to 200 residues = 3000 atoms so that the CPU oracle stays within seconds):
+    parameters of a long polymer, one graph, no_grad — what Grappa.predict runs."""
+    model, sd = build_model()
+    g = S.cfg3_graph(n_res=200, seed=1)
+    with torch.no_grad():
+        h_ref, p_ref = O.model_forward(sd, g)
+        gd = model(g.to(DEV))
+    np.testing.assert_allclose(gd.nodes["n1"].data["h"].cpu().numpy(), h_ref.numpy(), rtol=1e-4, atol=3e-5)
+    assert_params_close(graph_params(gd), p_ref, "cfg3")
+    assert gd.nodes["n4"].data["k"].shape == (g.num_nodes("n4"), 3)
+
+
+def test_cfg3_full_size_properties():
+    """Full 15,000-atom system: finite outputs, physical ranges of the range maps, permutation symmetry of the readout
+    (reversing a bond / angle / proper tuple leaves its parameters unchanged), determinism."""
+    model, _ = build_model()
+    g = S.cfg3_graph()
+    gd = g.to(DEV)
+    with torch.no_grad():
+        out = model(gd)
+    k2, eq2 = out.nodes["n2"].data["k"].clone(), out.nodes["n2"].data["eq"].clone()
+    k3, eq3 = out.nodes["n3"].data["k"].clone(), out.nodes["n3"].data["eq"].clone()
+    k4 = out.nodes["n4"].data["k"].clone()
+    for t in (k2, eq2, k3, eq3, k4, out.nodes["n4_improper"].data["k"]):
+        assert bool(torch.isfinite(t).all())
+    assert float(k2.min()) > 0 and float(eq2.min()) > 0 and float(k3.min()) > 0
+    assert 0 < float(eq3.min()) and float(eq3.max()) < 3.1416
+    g2 = S.cfg3_graph()
+    for lvl in ("n2", "n3", "n4"):
+        g2.nodes[lvl].data["idxs"] = g2.nodes[lvl].data["idxs"].flip(1).contiguous()
+    with torch.no_grad():
+        out2 = model(g2.to(DEV))
+    np.testing.assert_allclose(out2.nodes["n2"].data["k"].cpu().numpy(), k2.cpu().numpy(), rtol=2e-5, atol=1e-4)
+    np.testing.assert_allclose(out2.nodes["n3"].data["eq"].cpu().numpy(), eq3.cpu().numpy(), rtol=2e-5, atol=1e-6)
+    np.testing.assert_allclose(out2.nodes["n4"].data["k"].cpu().numpy(), k4.cpu().numpy(), rtol=1e-4, atol=2e-4 * K_STD_TORSION)
+    with torch.no_grad():
+        out3 = model(S.cfg3_graph().to(DEV))
+    assert torch.equal(out3.nodes["n2"].data["k"], k2) and torch.equal(out3.nodes["n4"].data["k"], k4), "not deterministic"

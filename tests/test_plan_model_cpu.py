@@ -71,7 +71,7 @@ def test_energy_plan_invariants(block_atoms):
     g = batch([S.trimer_molecule(s, 2) for s in (0, 1, 2)])
     p = build_plan(g, block_atoms=block_atoms)
     es = p.energy_sizes
-    blk = p.host_view("e_blk").reshape(-1, 8)
+    blk = p.host_view("e_blk").reshape(-1, 12)
     rec_atoms = p.host_view("e_rec_atoms").reshape(-1, 4)
     rec_meta = p.host_view("e_rec_meta").reshape(-1, 2)
     rec_slot = p.host_view("e_rec_slot").reshape(-1, 4)
@@ -108,6 +108,8 @@ def test_energy_plan_invariants(block_atoms):
                     a = idx[i]
                     assert rec_slot[r, i] in pull_slot[pull_ptr[a]:pull_ptr[a + 1]]
         assert sorted(seen_slots) == list(range(blk[b, 5]))     # slots are dense per block
+        lv = rec_meta[r0:r0 + nr, 0] & 3
+        assert [int((lv == l).sum()) for l in range(4)] == blk[b, 8:12].tolist()
         total_inc += len(seen_slots)
     for l in levels:
         assert (owners[l] == 1).all()       # every tuple's energy is counted exactly once
