@@ -51,6 +51,18 @@ DEFAULT_CONFIG = dict(   # configs/model/default.yaml
     shifted_elu=True)
 
 
+PARALLEL_WRITERS = True
+_WRITER_STREAMS = {}
+
+
+def _writer_streams(device):
+    st = _WRITER_STREAMS.get(device)
+    if st is None:
+        st = [torch.cuda.Stream(device=device) for _ in range(4)]
+        _WRITER_STREAMS[device] = st
+    return st
+
+
 def _unsupported(what: str):
     raise NotImplementedError(f"grappa_b200: {what} is outside the accelerated hot path (default-config family only)")
 
@@ -615,11 +627,26 @@ class WriteParameters(nn.Module):
                                                       only_n2=only_n2_improper, **common)
 
     def forward(self, g, plan):
-        """interaction_parameters.py:136-146."""
-        g = self.bond_writer(g, plan)
-        g = self.angle_writer(g, plan)
-        g = self.proper_writer(g, plan)
-        g = self.improper_writer(g, plan)
+        """interaction_parameters.py:136-146.  The four writers only share their input (the atom embedding), so they run
+        on four parallel streams (forked from / joined into the caller's stream; under CUDA-graph capture these become
+        parallel branches).  Their GEMMs have 20-100 tiles each, far fewer than the 148 SMs, so running them side by
+        side is what fills the machine.  Autograd replays each writer's backward on the stream of its forward."""
+        writers = (self.bond_writer, self.angle_writer, self.proper_writer, self.improper_writer)
+        h = g.nodes["n1"].data["h"]
+        if not (PARALLEL_WRITERS and h.is_cuda):
+            for w in writers:
+                g = w(g, plan)
+            return g
+        main = torch.cuda.current_stream(h.device)
+        streams = _writer_streams(h.device)
+        fork = torch.cuda.Event()
+        fork.record(main)
+        for w, st in zip(writers, streams):
+            st.wait_event(fork)
+            with torch.cuda.stream(st):
+                g = w(g, plan)
+        for st in streams:
+            main.wait_stream(st)
         return g
 
 

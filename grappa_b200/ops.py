@@ -72,10 +72,12 @@ WORKSPACE_FLOATS = 8 * 1024 * 1024       # 32 MB split-K scratch per device, all
 
 
 def _workspace(device):
-    ws = _WORKSPACE.get(device)
+    """Split-K scratch, one per (device, stream): GEMMs of the four parameter writers run on parallel streams."""
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WORKSPACE.get(key)
     if ws is None:
         ws = torch.empty(WORKSPACE_FLOATS, device=device, dtype=torch.float32)
-        _WORKSPACE[device] = ws
+        _WORKSPACE[key] = ws
     return ws
 
 
