@@ -18,6 +18,47 @@ ACT_NONE, ACT_ELU = 0, 1
 # (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
 # Valid because every parameter of the model is used exactly once per forward.
 GRAD_SINK = None
+# With a gradient sink nothing downstream in autograd consumes parameter gradients, so the weight-gradient GEMM, the
+# bias column sum and the LayerNorm affine reductions are issued on a side stream and overlap with the activation-
+# gradient chain (most of these kernels have far fewer tiles than SMs).  The step driver joins the side stream after
+# backward; tensors read by the side work are parked in _DEFERRED until then.
+_SIDE_STREAMS = {}
+_DEFERRED = []
+
+
+def _side_stream(device):
+    st = _SIDE_STREAMS.get(device)
+    if st is None:
+        st = torch.cuda.Stream(device=device)
+        _SIDE_STREAMS[device] = st
+    return st
+
+
+def join_side_work(device):
+    """Make the current stream wait for all side-stream gradient work; called once after backward."""
+    st = _SIDE_STREAMS.get(device)
+    if st is not None:
+        torch.cuda.current_stream(device).wait_stream(st)
+    _DEFERRED.clear()
+
+
+class _on_side_stream:
+    """Context: fork the side stream from the current one (everything issued so far is visible to it)."""
+    def __init__(self, device, keep):
+        self.device, self.keep = device, keep
+
+    def __enter__(self):
+        cur = torch.cuda.current_stream(self.device)
+        side = _side_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        side.wait_event(ev)
+        _DEFERRED.append(self.keep)
+        self.ctx = torch.cuda.stream(side)
+        self.ctx.__enter__()
+
+    def __exit__(self, *a):
+        self.ctx.__exit__(*a)
 
 
 def _stream():
@@ -146,20 +187,30 @@ class LinearFn(torch.autograd.Function):
         else:
             dz, lddz = dy, lddy
         dx = dw = None
+        w_tgt = sink.get(ctx.sink_ids[0]) if (sink is not None and ctx.needs_input_grad[1]) else None
+        b_sunk = want_db and sink is not None and sink.get(ctx.sink_ids[1]) is not None
+        side_ok = (not ctx.needs_input_grad[1] or w_tgt is not None) and (not want_db or b_sunk) and M > 0
+
+        def param_grads():
+            nonlocal dw
+            if ctx.needs_input_grad[1]:
+                dw = w_tgt if w_tgt is not None else torch.empty((N, K), device=dy.device, dtype=torch.float32)
+                gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
+                if w_tgt is not None:
+                    dw = None
+            if want_db and not db_done:
+                _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
+
+        if side_ok and (ctx.needs_input_grad[1] or (want_db and not db_done)):
+            with _on_side_stream(dy.device, (dz, x, scratch if want_db else None)):
+                param_grads()
+        else:
+            param_grads()
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
             gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
-        if ctx.needs_input_grad[1]:
-            tgt = sink.get(ctx.sink_ids[0]) if sink is not None else None
-            dw = tgt if tgt is not None else torch.empty((N, K), device=dy.device, dtype=torch.float32)
-            gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
-            if tgt is not None:
-                dw = None
-        if want_db:
-            if not db_done:
-                _lib.check(L.grappa_colsum(M, N, _p(dz), lddz, _p(db), _p(scratch), _stream()))
-            if sink is not None and sink.get(ctx.sink_ids[1]) is not None:
-                db = None
+        if b_sunk:
+            db = None
         dr = dy if ldc == N else dy[:, :N]
         return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,
                 dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None)

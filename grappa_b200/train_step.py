@@ -85,6 +85,7 @@ class TrainStep:
             loss = ops.MolwiseLossFn.apply(gd["energy"], n1["gradient"], g.nodes["n4"].data["k"], g.nodes["n4_improper"].data["k"],
                                            gd["energy_ref"], n1["gradient_ref"], gd.get("is_dummy"), plan, self.weights)
             loss.backward()
+            ops.join_side_work(self.device)
             self.seed_dev.add_(1)
         finally:
             ops.GRAD_SINK = None
