@@ -23,6 +23,16 @@ for p in (ROOT, os.path.join(ROOT, "oracle")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
+# stdout must carry exactly ONE JSON line: park the real stdout and point fd 1 at stderr, so that anything a library
+# prints there (e.g. NCCL's version banner) cannot get in front of the result
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 import torch  # noqa: E402
 
 MOLS_PER_RANK = 32
@@ -142,7 +152,7 @@ def run_reference(args):
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": "molecules/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -172,8 +182,6 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # NCCL writes its version banner / debug log to stdout by default; stdout must carry exactly one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         torch.distributed.init_process_group("nccl", device_id=dev)
     if args.math_mode is not None:
         ops.MATH_MODE = args.math_mode
@@ -272,7 +280,9 @@ def main():
                             "pipe": "fp32 FFMA (math_mode 0)" if ops.MATH_MODE == 0 else
                                     "tcgen05 kind::tf32, 3 MMAs per product (3xTF32): the pipe's own dense peak is 1/2 of bf16, "
                                     "so the fp32-accurate ceiling is 1/6 of the bf16 peak",
-                            "share_of_step": gemm_ms / step_ms, "launches_per_step": gm["calls"],
+                            "share_of_step": gemm_ms / tot, "launches_per_step": gm["calls"],
+                            "share_note": "share of the summed device time of this library's kernels; the step itself overlaps "
+                                          "kernels on parallel streams, so the sum exceeds the step time",
                             "flops_per_step": gm["flops"], "ms_per_step": gemm_ms,
                             "avg_launch_us": gemm_ms * 1e3 / gm["calls"],
                             "method": "the step's recorded launches replayed back to back in a CUDA graph, CUDA events"}
@@ -283,6 +293,13 @@ def main():
                 gbs = d["bytes"] / (dev_ms[name] * 1e-3) / 1e9
                 others[label] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
                                  "us_per_call": dev_ms[name] * 1e3 / d["calls"]}
+        try:     # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/)
+            with open(os.path.join(ROOT, "profiles", "r01_gemm_tc_traffic.json")) as f:
+                tr = json.load(f)
+            line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
+            line["roofline"]["traffic_note"] = tr["note"]
+        except Exception:
+            pass
         line["roofline_other_kernels"] = others
         line["kernel_ms_per_step"] = {k: round(v, 4) for k, v in sorted(dev_ms.items(), key=lambda kv: -kv[1])}
         line["kernel_ms_per_step"]["_sum_own_kernels"] = round(tot, 4)
@@ -299,7 +316,7 @@ def main():
     elif rank == 0:
         line["cpu_baseline"] = None
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
