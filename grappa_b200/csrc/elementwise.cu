@@ -206,16 +206,28 @@ __global__ void __launch_bounds__(256) colreduce_vec_kernel(ColArgs a) {
     }
 }
 
-// stage 2: out_k[col] = sum_chunks part_k[chunk][col]; blockIdx.y selects k
-__global__ void colreduce_stage2_vec_kernel(int64_t R, int64_t N, const float* __restrict__ part0, const float* __restrict__ part1,
-                                            float* __restrict__ out0, float* __restrict__ out1) {
-    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= N) return;
+// stage 2: out_k[col] = sum_chunks part_k[chunk][col]; blockIdx.y selects k.  32 columns x 8 chunk-lanes per CTA:
+// the chunk loop is 8-way parallel (the partials are L2-resident, the loop is latency-bound), the 8 lane sums are
+// combined in lane order, so the result is deterministic.
+__global__ void __launch_bounds__(256) colreduce_stage2_vec_kernel(int64_t R, int64_t N, const float* __restrict__ part0,
+                                                                   const float* __restrict__ part1, float* __restrict__ out0,
+                                                                   float* __restrict__ out1) {
+    __shared__ float sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t col = (int64_t)blockIdx.x * 32 + tx;
     const float* part = blockIdx.y == 0 ? part0 : part1;
     float* out = blockIdx.y == 0 ? out0 : out1;
     float s = 0.f;
-    for (int64_t r = 0; r < R; ++r) s += part[r * N + col];
-    out[col] = s;
+    if (col < N)
+        for (int64_t r = ty; r < R; r += 8) s += part[r * N + col];
+    sh[ty][tx] = s;
+    __syncthreads();
+    if (ty == 0 && col < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t += sh[j][tx];
+        out[col] = t;
+    }
 }
 
 // rows per chunk so that the stage-1 grid is about two waves of 148 SMs; multiple of 8 (the warps interleave rows)
@@ -421,7 +433,7 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
             dim3 grid((unsigned)ceil_div(D, 128), (unsigned)R);
             colreduce_vec_kernel<1><<<grid, 256, 0, st>>>(a);
             GRAPPA_CHECK_LAUNCH();
-            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 128), 2), 128, 0, st>>>(R, D, a.part0, a.part1, dgamma, dbeta);
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 32), 2), 256, 0, st>>>(R, D, a.part0, a.part1, dgamma, dbeta);
             GRAPPA_CHECK_LAUNCH();
         } else {
             const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
@@ -430,7 +442,7 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
             dim3 grid((unsigned)ceil_div(D, 32), (unsigned)R);
             colreduce_stage1_kernel<1><<<grid, 256, 0, st>>>(M, D, dY, lddy, X, ldx, mean, rstd, p0, p1);
             GRAPPA_CHECK_LAUNCH();
-            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 128), 2), 128, 0, st>>>(R, D, p0, p1, dgamma, dbeta);
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 32), 2), 256, 0, st>>>(R, D, p0, p1, dgamma, dbeta);
             GRAPPA_CHECK_LAUNCH();
         }
     }
@@ -452,7 +464,7 @@ extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, 
         a.M = M; a.N = N; a.X = X; a.ldx = ldx; a.part0 = scratch; a.rows_per_chunk = col_rows_per_chunk(M, N);
         colreduce_vec_kernel<0><<<dim3((unsigned)ceil_div(N, 128), (unsigned)R), 256, 0, st>>>(a);
         GRAPPA_CHECK_LAUNCH();
-        colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
+        colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
         GRAPPA_CHECK_LAUNCH();
         return 0;
     }
@@ -461,7 +473,7 @@ extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, 
     dim3 grid((unsigned)ceil_div(N, 32), (unsigned)R);
     colreduce_stage1_kernel<0><<<grid, 256, 0, st>>>(M, N, X, ldx, nullptr, 0, nullptr, nullptr, scratch, nullptr);
     GRAPPA_CHECK_LAUNCH();
-    colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
+    colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }
@@ -532,7 +544,7 @@ extern "C" int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_
         colreduce_vec_kernel<2><<<dim3((unsigned)ceil_div(N, 128), (unsigned)R), 256, 0, st>>>(a);
         GRAPPA_CHECK_LAUNCH();
         if (colsum_out) {
-            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 128), 1), 128, 0, st>>>(R, N, scratch, nullptr, colsum_out, nullptr);
+            colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(R, N, scratch, nullptr, colsum_out, nullptr);
             GRAPPA_CHECK_LAUNCH();
         }
         return 0;

@@ -424,15 +424,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     }
 }
 
-// split-K reduction: C = epilogue( sum_z partial[z] ), fixed summation order (deterministic)
-__global__ void splitk_reduce_kernel(GemmParams p, int splits, const float* __restrict__ partial) {
+// split-K reduction: C = epilogue( sum_z partial[z] ), fixed summation order (deterministic).  The slices are L2-resident
+// and the loop over them is latency-bound, so loads are issued four slices at a time before they are added in order.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmParams p, int splits, const float* __restrict__ partial) {
     const int64_t total = p.M * p.N;
     const bool has_drop = p.drop_p > 0.f;
     const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int64_t m = i / p.N, n = i % p.N;
         float z = 0.f;
-        for (int s = 0; s < splits; ++s) z += partial[(int64_t)s * total + i];
+        for (int s0 = 0; s0 < splits; s0 += 4) {
+            float t[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) t[u] = (s0 + u < splits) ? __ldcg(partial + (int64_t)(s0 + u) * total + i) : 0.f;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) z += t[u];
+        }
         if (p.bias) z += __ldg(p.bias + n);
         if (p.act == 1) z = elu1(z);
         if (has_drop) z = hash_uniform(seed, (uint64_t)i) >= p.drop_p ? z * p.drop_scale : 0.f;
