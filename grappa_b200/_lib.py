@@ -46,6 +46,7 @@ PROTOTYPES = {
     "grappa_energy_vjp": (I, [I64, P, P, P, P, P, I64, P, I64, P, I64, P, I64, P, P, P, P, P, I, P, I,
                               P, P, P, P, P, P, P]),
     "grappa_csr_build": (I, [I64, I64, P, P, P]),
+    "grappa_enumerate_tuples": (I, [I64, P, I64, P, P, P]),
     "grappa_molwise_loss": (I, [I64, I64, P, P, P, P, P, P, P, P, P, I, P, I, F, F, F, F, P, P, P, P, P, P, P, P]),
     "grappa_adamw": (I, [I64, P, P, P, P, F, F, F, F, F, I64, F, P]),
 }
@@ -126,7 +127,7 @@ class _ProfiledLib:
         fn = getattr(self._h, name)
         if not name.startswith("grappa_") or name in ("grappa_last_error", "grappa_launch_count", "grappa_abi_version",
                                                        "grappa_colsum_scratch_floats", "grappa_layernorm_bwd_scratch_floats",
-                                                       "grappa_csr_build", "grappa_energy_plan_build"):
+                                                       "grappa_csr_build", "grappa_energy_plan_build", "grappa_enumerate_tuples"):
             return fn
         prof = self._p
 

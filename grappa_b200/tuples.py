@@ -13,8 +13,11 @@ tuple layout that must be bit-exact"), so the sort keys below reproduce the refe
         for atom4 in sorted(neigh[atom3]) while atom4 < atom1, atom4 != atom2:
           proper (atom4, atom3, atom2, atom1)                     (:48-56)
 
-This is host-side index work (int64), not a GPU kernel.
+This is host-side index work (int64), not a GPU kernel.  `enumerate_tuples` runs the loop nest in C++ through the
+C ABI (`grappa_enumerate_tuples`, csrc/tuples.cu); `enumerate_tuples_numpy` is an independent sort-based derivation
+of the same layout kept as a cross-check for the tests.
 """
+import ctypes
 from typing import Dict, Sequence, Tuple
 
 import numpy as np
@@ -55,8 +58,28 @@ def enumerate_tuples(bonds: Sequence[Sequence[int]], n_atoms: int = None) -> Dic
     """
     bonds: (n_bonds, 2) atom indices in 0..n_atoms-1.
     Returns {'bonds': (n_bonds,2) with bond[0] < bond[1], 'angles': (n_angles,3), 'propers': (n_propers,4)} int64,
-    rows in the reference's order (see module docstring).
+    rows in the reference's order (see module docstring).  Raises ValueError on a self-bond.
     """
+    from . import _lib
+    bonds = np.ascontiguousarray(np.asarray(bonds, dtype=np.int64).reshape(-1, 2))
+    if n_atoms is None:
+        n_atoms = int(bonds.max()) + 1 if len(bonds) else 0
+    L = _lib.lib()
+    ptr = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    counts = np.zeros(2, np.int64)
+    rc = L.grappa_enumerate_tuples(len(bonds), ptr(bonds), int(n_atoms), ptr(counts), None, None)
+    if rc != 0:
+        raise ValueError(L.grappa_last_error().decode())
+    angles = np.empty((int(counts[0]), 3), np.int64)
+    propers = np.empty((int(counts[1]), 4), np.int64)
+    rc = L.grappa_enumerate_tuples(len(bonds), ptr(bonds), int(n_atoms), ptr(counts), ptr(angles), ptr(propers))
+    if rc != 0:
+        raise ValueError(L.grappa_last_error().decode())
+    return {"bonds": np.sort(bonds, axis=1), "angles": angles, "propers": propers}
+
+
+def enumerate_tuples_numpy(bonds: Sequence[Sequence[int]], n_atoms: int = None) -> Dict[str, np.ndarray]:
+    """Sort-based derivation of the same rows (no loop nest): cross-check for `enumerate_tuples`."""
     bonds = np.asarray(bonds, dtype=np.int64).reshape(-1, 2)
     if n_atoms is None:
         n_atoms = int(bonds.max()) + 1 if len(bonds) else 0

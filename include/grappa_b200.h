@@ -208,6 +208,15 @@ int grappa_energy_vjp(int64_t C, const float* xyz, const float* gE, const float*
  * their original order.  Used for CSR-by-destination / by-source of the bond edges and the atom -> token incidence. */
 int grappa_csr_build(int64_t n, int64_t n_keys, const int64_t* keys, int32_t* ptr, int32_t* order);
 
+/* Interaction-tuple enumeration from the bond list; replaces utils/tuple_indices.py:8-70 (get_idx_tuples) and
+ * :73-110 (get_neighbor_dict).  bonds: (n_bonds,2) int64 atom rows in [0,n_atoms).  Rows come out in the reference's
+ * order: outer loop over atoms in first-appearance order of the flattened bond list, sorted neighbour lists, angle
+ * (a1,a2,a3) kept when a1 < a3, proper (a4,a3,a2,a1) for a4 < a1, a4 != a2.  Two calls: with angles == propers ==
+ * NULL only counts[0] (angles) and counts[1] (propers) are written; with both given, counts holds their capacities
+ * (rows) on entry and the row counts on return.  Self-bonds are an error (reference: assertion at :85). */
+int grappa_enumerate_tuples(int64_t n_bonds, const int64_t* bonds, int64_t n_atoms, int64_t* counts,
+                            int64_t* angles, int64_t* propers);
+
 /* Training-side fused kernels (next rows of SURVEY.md §8f, used by the data-parallel step driver). */
 /* Molecule-wise loss (training/loss.py:51-174 with param_weight 0): forward value and gradients w.r.t. energy,
  * gradient and the torsion force constants in one pass.  loss_parts: (n_mol) per-molecule terms (already / n_mol);

@@ -227,3 +227,20 @@ def test_cfg3_full_size_properties():
     with torch.no_grad():
         out3 = model(S.cfg3_graph().to(DEV))
     assert torch.equal(out3.nodes["n2"].data["k"], k2) and torch.equal(out3.nodes["n4"].data["k"], k4), "not deterministic"
+
+
+def test_python_default_config_ungated_torsions():
+    """GrappaModel() Python defaults differ from the YAML (models/grappa.py:28-29): ungated torsions with the mean shift
+    and n_periodicity_improper = 3 (only n = 2 predicted)."""
+    m = GrappaModel()
+    sd = m.state_dict()
+    deterministic_fill_(sd)
+    m.load_state_dict(sd)
+    m = m.to(DEV).eval()
+    g = batch([S.trimer_molecule(s, 2) for s in (0, 1)])
+    with torch.no_grad():
+        h_ref, p_ref = O.model_forward({k: v.clone() for k, v in sd.items()}, g)
+        gd = m(g.to(DEV))
+    assert gd.nodes["n4_improper"].data["k"].shape == (48, 3)
+    assert float(gd.nodes["n4_improper"].data["k"][:, [0, 2]].abs().max()) == 0.0
+    assert_params_close(graph_params(gd), p_ref, "python-default config")

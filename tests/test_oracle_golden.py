@@ -89,3 +89,31 @@ def test_batch3_loss_and_grads_match_reference(golden_dir):
         np.testing.assert_allclose(mine[3:], dg[3:], rtol=2e-3, atol=scale * 2e-2, err_msg=name)
     for name in gold["grad_none"]:
         assert sd[str(name)].grad is None
+
+
+@pytest.mark.reference
+def test_python_default_config_matches_live_reference():
+    """GrappaModel() with the Python defaults (ungated torsions, n_periodicity_improper = 3: models/grappa.py:28-29)
+    against the live reference; skipped where /root/reference is absent."""
+    import reference_loader as rl
+    if not rl.reference_available():
+        pytest.skip("reference tree not present")
+    rl.load_reference()
+    from grappa.models.grappa import GrappaModel as RefModel
+    from make_golden import to_reference_graph
+    from grappa_b200.model import GrappaModel
+    torch.set_float32_matmul_precision("highest")
+    ref = RefModel().eval()
+    mine = GrappaModel()
+    sd = ref.state_dict()
+    assert list(sd.keys()) == list(mine.state_dict().keys())
+    deterministic_fill_(sd)
+    ref.load_state_dict(sd)
+    hg = S.cfg1_graph(n_confs=2, seed=3)
+    with torch.no_grad():
+        g = ref(to_reference_graph(hg))
+        h, params = O.model_forward({k: v.clone() for k, v in sd.items()}, hg)
+    for lvl in O.LEVELS:
+        for key, v in params[lvl].items():
+            np.testing.assert_allclose(v.numpy(), g.nodes[lvl].data[key].numpy(), rtol=1e-5, atol=1e-6, err_msg=f"{lvl} {key}")
+    assert params["n4_improper"]["k"].shape == (12, 3)

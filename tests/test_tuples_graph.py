@@ -8,7 +8,7 @@ import torch
 
 from grappa_b200 import synthetic as S
 from grappa_b200.graph import batch, unbatch
-from grappa_b200.tuples import enumerate_tuples, improper_rows
+from grappa_b200.tuples import enumerate_tuples, enumerate_tuples_numpy, improper_rows
 
 
 def test_tuples_match_golden(golden_dir):
@@ -22,6 +22,29 @@ def test_tuples_match_golden(golden_dir):
         nb = S._neighbour_lists(bonds, n)
         cen = gold[name + "_centres"]
         np.testing.assert_array_equal(improper_rows(cen, [nb[c] for c in cen.tolist()]), gold[name + "_impropers"])
+
+
+def test_cxx_and_numpy_enumerations_agree_on_random_graphs():
+    rng = np.random.default_rng(0)
+    for trial in range(20):
+        n = int(rng.integers(3, 60))
+        # random tree plus a few ring-closing bonds, atoms relabelled so that first-appearance order != index order
+        perm = rng.permutation(n)
+        bonds = [(perm[i], perm[int(rng.integers(0, i))]) for i in range(1, n)]
+        have = {tuple(sorted(b)) for b in bonds}
+        for _ in range(int(rng.integers(0, 4))):
+            a, b = (int(x) for x in rng.choice(n, 2, replace=False))
+            if (min(a, b), max(a, b)) not in have:
+                have.add((min(a, b), max(a, b)))
+                bonds.append((a, b))
+        bonds = np.array(bonds, np.int64)[rng.permutation(len(bonds))]
+        a, b = enumerate_tuples(bonds, n), enumerate_tuples_numpy(bonds, n)
+        for k in ("bonds", "angles", "propers"):
+            np.testing.assert_array_equal(a[k], b[k], err_msg=f"trial {trial} {k}")
+        # every angle / proper is a path along bonds, each equivalence class appears once
+        assert len({tuple(r) for r in a["angles"].tolist()} | {tuple(r[::-1]) for r in a["angles"].tolist()}) == 2 * len(a["angles"])
+        for r in a["propers"].tolist():
+            assert all((min(x, y), max(x, y)) in have for x, y in zip(r[:-1], r[1:])) and r[0] < r[3]
 
 
 def test_survey_sizes():
