@@ -308,6 +308,7 @@ def main():
     # ---- side measurements on rank 0: inference (cfg 3) and energy sweep (cfg 4) ----
     if rank == 0 and world == 1 and not args.no_extras:
         line["extra"] = extras(dev, pk)
+        line["extra"]["device_collate"] = collate_bench(ts, dev, K)
     if world > 1:
         torch.distributed.barrier()
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -320,6 +321,48 @@ def main():
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
+
+
+def collate_bench(ts, dev, K):
+    """the same training step, but every batch is a different set of molecules assembled ON THE
+    DEVICE from a resident per-molecule store (store.MoleculeStore), against the host collate of the same batch."""
+    import time
+    import numpy as np
+    from grappa_b200 import synthetic as S
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.graph import batch
+    from grappa_b200.store import MoleculeStore
+    mols = S.cfg2_graphs(3 * MOLS_PER_RANK, N_CONFS, first_seed=1000)
+    store = MoleculeStore(mols, dev)
+    rng = np.random.default_rng(0)
+    draws = [rng.choice(len(mols), MOLS_PER_RANK, replace=False) for _ in range(K + 6)]
+    for ids in draws[:6]:                              # warm-up incl. CUDA-graph capture for this batch shape
+        ts.step_from_store(store, ids)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h2d = 0
+    a.record()
+    for ids in draws[6:]:
+        loss = ts.step_from_store(store, ids)
+    last = loss.item()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / K
+    spec = store.prepare(draws[0])
+    t0 = time.perf_counter()
+    n_host = 5
+    for ids in draws[:n_host]:
+        PackedBatch(batch([mols[i] for i in ids]), pin=False)
+    host_ms = (time.perf_counter() - t0) / n_host * 1e3
+    t0 = time.perf_counter()
+    for ids in draws[:n_host]:
+        store.prepare(ids)
+    prep_ms = (time.perf_counter() - t0) / n_host * 1e3
+    return {"molecules_per_s": MOLS_PER_RANK / (ms * 1e-3), "ms_per_step": ms, "h2d_bytes_per_step": spec.h2d_bytes,
+            "store_molecules": len(mols), "store_bytes": store.nbytes, "host_prepare_ms_per_batch": prep_ms,
+            "host_collate_ms_per_batch_1_thread": host_ms, "final_loss": last,
+            "note": "every step draws 32 different molecules; batch assembled by grappa_collate_float/int from the HBM-resident "
+                    "store; the host uploads only the segment tables"}
 
 
 def extras(dev, pk):

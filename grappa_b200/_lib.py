@@ -47,6 +47,8 @@ PROTOTYPES = {
                               P, P, P, P, P, P, P]),
     "grappa_csr_build": (I, [I64, I64, P, P, P]),
     "grappa_enumerate_tuples": (I, [I64, P, I64, P, P, P]),
+    "grappa_collate_int": (I, [I64, P, P, P, P, P]),
+    "grappa_collate_float": (I, [I64, P, P, P, P, P]),
     "grappa_molwise_loss": (I, [I64, I64, P, P, P, P, P, P, P, P, P, I, P, I, F, F, F, F, P, P, P, P, P, P, P, P]),
     "grappa_adamw": (I, [I64, P, P, P, P, F, F, F, F, F, I64, F, P]),
 }

@@ -59,15 +59,24 @@ class PackedBatch:
     def h2d_bytes(self) -> int:
         return int(self.fbuf.numel()) * 4 + self.plan.h2d_bytes
 
+    @property
+    def n_float(self) -> int:
+        return int(self.fbuf.numel())
+
+    @property
+    def n_int(self) -> int:
+        return int(self.plan.host.numel())
+
 
 class DeviceBatch:
-    """Static device buffers + a HeteroGraph whose tensors are views into them."""
+    """Static device buffers + a HeteroGraph whose tensors are views into them.  `packed` is a `PackedBatch` (filled by
+    two host->device copies) or a `store.CollatedSpec` (filled on the device by `MoleculeStore.collate_into`)."""
 
-    def __init__(self, packed: PackedBatch, device):
+    def __init__(self, packed, device):
         self.device = torch.device(device)
         self.signature = packed.signature
-        self.fbuf = torch.empty_like(packed.fbuf, device=self.device)
-        self.ibuf = torch.empty_like(packed.plan.host, device=self.device)
+        self.fbuf = torch.empty(packed.n_float, dtype=torch.float32, device=self.device)
+        self.ibuf = torch.empty(packed.n_int, dtype=torch.int32, device=self.device)
         plan = BatchPlan()
         plan.__dict__.update(packed.plan.__dict__)
         plan.dev = self.ibuf
@@ -82,7 +91,8 @@ class DeviceBatch:
                 g.nodes[lvl].data["idxs"] = plan.view("idx_" + lvl).view(-1, {"n2": 2, "n3": 3}.get(lvl, 4))
         g._plan_cache["plan"] = plan
         self.graph = g
-        self.load(packed)
+        if isinstance(packed, PackedBatch):
+            self.load(packed)
 
     def load(self, packed: PackedBatch, non_blocking: bool = True):
         """Two host->device copies on the current stream."""

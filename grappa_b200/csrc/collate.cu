@@ -1,0 +1,102 @@
+// Device-side collate: assembles a batch's two static device buffers (fp32 fields, int32 batch
+// plan) from a packed per-molecule store that already lives in HBM.  Replaces, per step, the host work of
+// data/graph_data_loader.py:23-73 (conformation sub-/over-sampling with is_dummy padding via
+// utils/dgl_utils.py:137-176) and utils/dgl_utils.py:11-63 (idxs offsetting + concatenation), plus this repo's own
+// host plan build: every per-molecule plan array composes under batching by adding an offset, so the batch plan is a
+// concatenation with per-segment addends.
+//
+// Both kernels are driven by a segment table (one row of 8 int64 per (array, molecule)); one CTA per segment.
+// HBM-bound byte movement: coalesced reads of the store, coalesced writes of the batch buffers.
+#include "common.cuh"
+
+namespace grappa {
+
+constexpr int kSeg = 8;   // int64 per segment row
+
+// int segments: [src, dst, len, mode, a0, a1, a2, a3]
+//   mode 0: out[i] = store[src+i] + a0
+//   mode 1: energy block rows (12 ints): col 0 += a0 (atom), col 2 += a1 (molecule), col 3 += a2 (record)
+//   mode 2: record meta pairs (level|owner, tuple): tuple += a[level]
+//   mode 3: record atoms (4 per record): += a0 where position < n_seq(level); level from store[a1 + 2*record]
+//   mode 4: out[i] = a0
+//   mode 5: out[i] = lit[src+i]                       (literals uploaded with the table: per-molecule offsets)
+__global__ void __launch_bounds__(256) collate_int_kernel(const int64_t* __restrict__ seg, const int32_t* __restrict__ store,
+                                                          const int32_t* __restrict__ lit, int32_t* __restrict__ out) {
+    const int64_t* s = seg + (int64_t)blockIdx.x * kSeg;
+    const int64_t src = s[0], dst = s[1], len = s[2];
+    const int mode = (int)s[3];
+    const int32_t a0 = (int32_t)s[4], a1 = (int32_t)s[5], a2 = (int32_t)s[6], a3 = (int32_t)s[7];
+    for (int64_t i = threadIdx.x; i < len; i += blockDim.x) {
+        int32_t v;
+        switch (mode) {
+            case 0: v = store[src + i] + a0; break;
+            case 1: {
+                const int c = (int)(i % 12);
+                v = store[src + i] + (c == 0 ? a0 : c == 2 ? a1 : c == 3 ? a2 : 0);
+                break;
+            }
+            case 2: {
+                v = store[src + i];
+                if (i & 1) {
+                    const int lvl = store[src + i - 1] & 3;
+                    v += lvl == 0 ? a0 : lvl == 1 ? a1 : lvl == 2 ? a2 : a3;
+                }
+                break;
+            }
+            case 3: {
+                const int lvl = store[s[5] + 2 * (i >> 2)] & 3;
+                const int n_seq = lvl == 0 ? 2 : lvl == 1 ? 3 : 4;
+                v = store[src + i] + (((int)(i & 3) < n_seq) ? a0 : 0);
+                break;
+            }
+            case 4: v = a0; break;
+            default: v = lit[src + i]; break;
+        }
+        out[dst + i] = v;
+    }
+}
+
+// float segments: [src, dst, rows, inner, C_src, C_dst, conf_off, mode]
+//   mode 0: out[dst + (r*C_dst + c)*inner + j] = store[src + (r*C_src + conf[conf_off + c])*inner + j]
+//           (conf_off < 0: identity, C_src == C_dst)
+//   mode 1: out[dst + c] = c >= C_src ? 1 : 0 for c < C_dst                 (is_dummy flags)
+__global__ void __launch_bounds__(256) collate_float_kernel(const int64_t* __restrict__ seg, const int32_t* __restrict__ conf,
+                                                            const float* __restrict__ store, float* __restrict__ out) {
+    const int64_t* s = seg + (int64_t)blockIdx.x * kSeg;
+    const int64_t src = s[0], dst = s[1], rows = s[2], inner = s[3], Cs = s[4], Cd = s[5], coff = s[6];
+    if (s[7] == 1) {
+        for (int64_t c = threadIdx.x; c < Cd; c += blockDim.x) out[dst + c] = c >= Cs ? 1.f : 0.f;
+        return;
+    }
+    const int64_t per_row = Cd * inner, total = rows * per_row;
+    for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+        const int64_t r = i / per_row, rem = i - r * per_row;
+        const int64_t c = rem / inner, j = rem - c * inner;
+        const int64_t cs = coff < 0 ? c : (int64_t)conf[coff + c];
+        out[dst + i] = store[src + (r * Cs + cs) * inner + j];
+    }
+}
+
+}  // namespace grappa
+
+using namespace grappa;
+
+extern "C" int grappa_collate_int(int64_t n_seg, const int64_t* seg, const int32_t* store, const int32_t* lit, int32_t* out,
+                                  void* stream) {
+    GRAPPA_CHECK_ARG(n_seg >= 0 && n_seg < 2147483647LL, "bad segment count");
+    if (n_seg == 0) return 0;
+    GRAPPA_CHECK_ARG(seg && store && out, "null pointer");
+    collate_int_kernel<<<(unsigned)n_seg, 256, 0, (cudaStream_t)stream>>>(seg, store, lit, out);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_collate_float(int64_t n_seg, const int64_t* seg, const int32_t* conf, const float* store, float* out,
+                                    void* stream) {
+    GRAPPA_CHECK_ARG(n_seg >= 0 && n_seg < 2147483647LL, "bad segment count");
+    if (n_seg == 0) return 0;
+    GRAPPA_CHECK_ARG(seg && store && out, "null pointer");
+    collate_float_kernel<<<(unsigned)n_seg, 256, 0, (cudaStream_t)stream>>>(seg, conf, store, out);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}

@@ -219,6 +219,46 @@ def delete_dummy_confs(g: HeteroGraph) -> HeteroGraph:
     return g
 
 
+def conf_indices(confs_present: int, num_confs: int, generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """Which stored conformations fill the `num_confs` slots of a batch (utils/dgl_utils.py:147-162): all of them in
+    order when the counts agree, a random subset (`randperm[:num_confs]`) when there are more, all followed by repeats
+    of the last one (flagged as dummies) when there are fewer."""
+    if confs_present == num_confs:
+        return torch.arange(num_confs)
+    if confs_present > num_confs:
+        return torch.randperm(confs_present, generator=generator)[:num_confs]
+    return torch.cat((torch.arange(confs_present), torch.full((num_confs - confs_present,), confs_present - 1, dtype=torch.long)))
+
+
+def set_number_confs(g: HeteroGraph, num_confs: int, generator: Optional[torch.Generator] = None,
+                     conf_idxs: Optional[torch.Tensor] = None) -> HeteroGraph:
+    """Reference: utils/dgl_utils.py:137-176.  Returns a NEW graph (the input is not mutated) whose conformation axis has
+    length `num_confs`; `g.nodes['g'].data['is_dummy']` marks padded slots.  `conf_idxs` overrides the random choice."""
+    if "xyz" not in g.nodes["n1"].data:
+        return g
+    present = g.nodes["n1"].data["xyz"].shape[1]
+    if conf_idxs is None:
+        conf_idxs = conf_indices(present, num_confs, generator)
+    out = HeteroGraph(dict(g._num_nodes), g._edges, {k: v.clone() for k, v in g._batch_num_nodes.items()})
+    for nt in g.ntypes:
+        out.nodes[nt].data.update(g.nodes[nt].data)
+    gd, n1 = out.nodes["g"].data, out.nodes["n1"].data
+    dummy = torch.zeros((1, num_confs), dtype=torch.float32)
+    if present < num_confs:
+        dummy[0, present:] = 1.0
+    gd["is_dummy"] = dummy
+    n1["xyz"] = n1["xyz"][:, conf_idxs]
+    for k in list(gd.keys()):
+        if "energy" in k:
+            gd[k] = gd[k][:, conf_idxs]
+            if torch.isnan(gd[k]).any():
+                raise RuntimeError(f"Found nan in {k} after setting number of conformations to {num_confs}")
+    for k in list(n1.keys()):
+        if "gradient" in k:
+            n1[k] = n1[k][:, conf_idxs]
+    return out
+
+
 def get_bond_edges(g):
     """(src, dst) of the directed bond edges for either container type."""
     try:

@@ -134,6 +134,17 @@ class TrainStep:
                                            self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
                                            getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
 
+    def step_from_store(self, store, mol_ids, conf_strategy="max", generator=None) -> torch.Tensor:
+        """One optimisation step on a batch collated ON THE DEVICE from a resident `store.MoleculeStore`: the host only
+        uploads the segment tables (tens of kB), not the batch."""
+        spec = store.prepare(mol_ids, conf_strategy, generator)
+        st = self._state_for(spec)
+        store.collate_into(spec, st["batch"])
+        loss = self.compute_gradients(spec, load=False)
+        self.all_reduce_gradients()
+        self.optimizer_step()
+        return loss
+
     def step(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
         loss = self.compute_gradients(packed, load=load)
         self.all_reduce_gradients()

@@ -217,6 +217,22 @@ int grappa_csr_build(int64_t n, int64_t n_keys, const int64_t* keys, int32_t* pt
 int grappa_enumerate_tuples(int64_t n_bonds, const int64_t* bonds, int64_t n_atoms, int64_t* counts,
                             int64_t* angles, int64_t* propers);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * Device-side collate.  Replaces, per training step, the host collate of
+ * data/graph_data_loader.py:23-73 (conformation sub-/over-sampling, is_dummy padding: utils/dgl_utils.py:137-176) and
+ * utils/dgl_utils.py:11-63 (idxs offsetting + concatenation) by two gather launches over a packed per-molecule store
+ * that is resident in HBM.  seg: device (n_seg,8) int64 segment rows, one CTA each:
+ *   int rows   [src, dst, len, mode, a0, a1, a2, a3]   mode 0 copy+a0 | 1 energy-block rows (col0+a0, col2+a1, col3+a2)
+ *              | 2 record meta (tuple += a[level]) | 3 record atoms (+a0 where pos < n_seq; a1 = store offset of the
+ *              molecule's record meta) | 4 fill a0 | 5 copy from lit[src..]
+ *   float rows [src, dst, rows, inner, C_src, C_dst, conf_off, mode]   mode 0 gather conformations conf[conf_off+c]
+ *              (conf_off < 0: identity) | 1 is_dummy flags (c >= C_src).
+ * store / out: device buffers (src / dst are element offsets into them); lit, conf: device int32. */
+int grappa_collate_int(int64_t n_seg, const int64_t* seg, const int32_t* store, const int32_t* lit, int32_t* out,
+                       void* stream);
+int grappa_collate_float(int64_t n_seg, const int64_t* seg, const int32_t* conf, const float* store, float* out,
+                         void* stream);
+
 /* Training-side fused kernels (next rows of SURVEY.md §8f, used by the data-parallel step driver). */
 /* Molecule-wise loss (training/loss.py:51-174 with param_weight 0): forward value and gradients w.r.t. energy,
  * gradient and the torsion force constants in one pass.  loss_parts: (n_mol) per-molecule terms (already / n_mol);
