@@ -89,6 +89,17 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
     return d;
 }
 
+// Explicit shared-state-space accesses: the tile pointers come from an integer-aligned base, so plain C++ dereferences
+// compile to GENERIC ld/st (LD.E / ST.E), which the compiler also has to keep in program order (possible aliasing).
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 // round-to-nearest fp32 -> tf32 (low 13 mantissa bits zero): unbiased split errors, exact operands for the tensor core
 __device__ __forceinline__ float tf32_rn(float x) {
     uint32_t r;
@@ -126,6 +137,65 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
           "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr));
+}
+
+// Write-out of one fully interior, 16-byte aligned tile, specialised at compile time on the epilogue flags: straight
+// loads -> math -> stores without per-element bounds / alignment branches (the general path below costs ~3 us per tile
+// in taken branches alone; this one ~0.5 us).  Rows are split over the ten warps, four rows in flight per pass.
+template <int NRES, bool ACT, bool DROP>
+__device__ __forceinline__ void writeout_interior(const GemmParams& p, uint32_t tile, int warp, int lane, int m0, int n0,
+                                                  uint64_t seed) {
+    constexpr int RPI = 4, PASS = (THREADS / 32) * RPI;
+    const int64_t n = (int64_t)n0 + lane * 4;
+    float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.bias) bv = __ldg(reinterpret_cast<const float4*>(p.bias + n));
+    const int64_t mrow = (int64_t)m0 + warp * RPI;
+    float* cp = p.C + mrow * p.ldc + n;
+    const float* r1 = NRES >= 1 ? p.res1 + mrow * p.ldr1 + n : nullptr;
+    const float* r2 = NRES >= 2 ? p.res2 + mrow * p.ldr2 + n : nullptr;
+    uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
+#pragma unroll 1
+    for (int r0 = warp * RPI; r0 < BM; r0 += PASS) {
+        float4 a[RPI], q1[RPI], q2[RPI];
+#pragma unroll
+        for (int i = 0; i < RPI; ++i) {
+            a[i] = lds128(ts + i * (EPI_LD * 4));
+            if (NRES >= 1) q1[i] = __ldg(reinterpret_cast<const float4*>(r1 + i * p.ldr1));
+            if (NRES >= 2) q2[i] = __ldg(reinterpret_cast<const float4*>(r2 + i * p.ldr2));
+        }
+#pragma unroll
+        for (int i = 0; i < RPI; ++i) {
+            float v[4] = {a[i].x + bv.x, a[i].y + bv.y, a[i].z + bv.z, a[i].w + bv.w};
+            if (ACT) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] = elu1(v[j]);
+            }
+            if (DROP) {
+                const uint64_t e0 = (uint64_t)(((int64_t)m0 + r0 + i) * p.N + n);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) v[j] = hash_uniform(seed, e0 + j) >= p.drop_p ? v[j] * p.drop_scale : 0.f;
+            }
+            if (NRES >= 1) { v[0] += q1[i].x; v[1] += q1[i].y; v[2] += q1[i].z; v[3] += q1[i].w; }
+            if (NRES >= 2) { v[0] += q2[i].x; v[1] += q2[i].y; v[2] += q2[i].z; v[3] += q2[i].w; }
+            *reinterpret_cast<float4*>(cp + i * p.ldc) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+        ts += PASS * (EPI_LD * 4);
+        cp += PASS * p.ldc;
+        if (NRES >= 1) r1 += PASS * p.ldr1;
+        if (NRES >= 2) r2 += PASS * p.ldr2;
+    }
+}
+
+template <int NRES>
+__device__ __forceinline__ void writeout_interior_dispatch(const GemmParams& p, uint32_t tile, int warp, int lane, int m0, int n0,
+                                                           uint64_t seed, bool act, bool drop) {
+    if (act) {
+        if (drop) writeout_interior<NRES, true, true>(p, tile, warp, lane, m0, n0, seed);
+        else writeout_interior<NRES, true, false>(p, tile, warp, lane, m0, n0, seed);
+    } else {
+        if (drop) writeout_interior<NRES, false, true>(p, tile, warp, lane, m0, n0, seed);
+        else writeout_interior<NRES, false, false>(p, tile, warp, lane, m0, n0, seed);
+    }
 }
 
 // A_MN / B_MN: operand is MN-major (rows of the global matrix run along k, m/n contiguous)
@@ -229,8 +299,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     const uint64_t dbh = make_desc(b_hi + bo, b_lbo, b_sbo, b_lt);
                     // B_lo sits directly behind B_hi in the stage, with the same row-group / atom strides, so one N = 256
                     // MMA yields A_hi*B_hi (columns 0..127) and A_hi*B_lo (columns 128..255); A_lo*B_hi joins the latter.
+#ifndef GRAPPA_TC_SKIP_MMA          // (debug builds only: isolates the TMA + split pipeline)
                     umma_tf32(tmem_buf, dah, dbh, idesc2, !(chunk_start && k == 0));
+#ifndef GRAPPA_TC_SKIP_MMA2
                     umma_tf32(tmem_buf + BN, dal, dbh, idesc, 1);
+#endif
+#else
+                    (void)dah; (void)dal; (void)dbh; (void)idesc2;
+#endif
                     (void)b_lo;
                 }
                 umma_commit(&empty[s]);          // frees the stage once these MMAs have read it
@@ -245,32 +321,38 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             mbar_wait(&full[s], (kb / STAGES) & 1);
             STAMP(2, threadIdx.x == 64 && kb == 0);
             uint8_t* st = smem + s * STAGE_BYTES;
+#ifndef GRAPPA_TC_SKIP_SPLIT        // (debug builds only: isolates the TMA + MMA pipeline)
+            const uint32_t st_a = smem_u32(st);
+            (void)st;
 #pragma unroll
             for (int op = 0; op < 2; ++op) {
-                float4* hi = reinterpret_cast<float4*>(st + op * 2 * TILE_BYTES);
-                float4* lo = reinterpret_cast<float4*>(st + op * 2 * TILE_BYTES + TILE_BYTES);
+                const uint32_t hi = st_a + op * 2 * TILE_BYTES + wt * 16, lo = hi + TILE_BYTES;
+                constexpr int NV = TILE_BYTES / 16 / 128;      // 8 float4 per thread and operand
+                float4 x[NV];
 #pragma unroll
-                for (int i = 0; i < TILE_BYTES / 16 / 128; ++i) {
-                    const int o = wt + i * 128;
-                    const float4 x = hi[o];
+                for (int i = 0; i < NV; ++i) x[i] = lds128(hi + i * 2048);     // all loads in flight before the first use
+#pragma unroll
+                for (int i = 0; i < NV; ++i) {
                     float4 h, l;
 #ifndef GRAPPA_TC_STORE_HI
-                    // (measured: identical accuracy, 13-15 % faster mainloop) the tensor core reads only the top 19 bits of the raw fp32 word, i.e. hi = trunc(x): leave the raw
-                    // tile in place (no write-back) and make lo relative to that truncation
-                    h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = tf32_rn(x.x - h.x);
-                    h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = tf32_rn(x.y - h.y);
-                    h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = tf32_rn(x.z - h.z);
-                    h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = tf32_rn(x.w - h.w);
+                    // (measured: identical accuracy, 13-15 % faster mainloop) the tensor core reads only the top 19 bits
+                    // of the raw fp32 word, i.e. hi = trunc(x): leave the raw tile in place (no write-back) and make lo
+                    // relative to that truncation
+                    h.x = __uint_as_float(__float_as_uint(x[i].x) & 0xFFFFE000u); l.x = tf32_rn(x[i].x - h.x);
+                    h.y = __uint_as_float(__float_as_uint(x[i].y) & 0xFFFFE000u); l.y = tf32_rn(x[i].y - h.y);
+                    h.z = __uint_as_float(__float_as_uint(x[i].z) & 0xFFFFE000u); l.z = tf32_rn(x[i].z - h.z);
+                    h.w = __uint_as_float(__float_as_uint(x[i].w) & 0xFFFFE000u); l.w = tf32_rn(x[i].w - h.w);
 #else
-                    h.x = tf32_rn(x.x); l.x = tf32_rn(x.x - h.x);
-                    h.y = tf32_rn(x.y); l.y = tf32_rn(x.y - h.y);
-                    h.z = tf32_rn(x.z); l.z = tf32_rn(x.z - h.z);
-                    h.w = tf32_rn(x.w); l.w = tf32_rn(x.w - h.w);
-                    hi[o] = h;
+                    h.x = tf32_rn(x[i].x); l.x = tf32_rn(x[i].x - h.x);
+                    h.y = tf32_rn(x[i].y); l.y = tf32_rn(x[i].y - h.y);
+                    h.z = tf32_rn(x[i].z); l.z = tf32_rn(x[i].z - h.z);
+                    h.w = tf32_rn(x[i].w); l.w = tf32_rn(x[i].w - h.w);
+                    sts128(hi + i * 2048, h);
 #endif
-                    lo[o] = l;
+                    sts128(lo + i * 2048, l);
                 }
             }
+#endif
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
             mbar_arrive(&split[s]);
         }
@@ -288,13 +370,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             STAMP(4, threadIdx.x == 192 && c == n_chunks - 1);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-            for (int cb = 0; cb < BN / 32; ++cb) {
-                uint32_t r[32], x[32];
-                tmem_ld32(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + cb * 32), r);
-                tmem_ld32(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + BN + cb * 32), x);
+            for (int cb = 0; cb < BN / 16; ++cb) {          // 16 columns at a time: 128 accumulators + 32 in flight fit the register file
+                uint32_t r[16], x[16];
+                tmem_ld16(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + cb * 16), r);
+                tmem_ld16(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + BN + cb * 16), x);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 32; ++j) acc[cb * 32 + j] += __uint_as_float(r[j]) + __uint_as_float(x[j]);
+                for (int j = 0; j < 16; ++j) acc[cb * 16 + j] += __uint_as_float(r[j]) + __uint_as_float(x[j]);
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive(&chunk_empty[buf]);
@@ -303,12 +385,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         // different rows per warp instruction.  Stage the tile in shared memory (all pipeline stages are idle once the
         // last slice has been committed), then let each warp stream whole rows: 512 contiguous bytes per instruction.
         STAMP(5, threadIdx.x == 192);
-        float* tile = reinterpret_cast<float*>(smem);                     // [128][EPI_LD]
         {
-            float* row = tile + (q * 32 + lane) * EPI_LD;
+            const uint32_t row = smem_u32(smem) + (q * 32 + lane) * EPI_LD * 4;    // tile [128][EPI_LD]
 #pragma unroll
             for (int j4 = 0; j4 < BN / 4; ++j4)
-                *reinterpret_cast<float4*>(row + j4 * 4) = make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]);
+                sts128(row + j4 * 16, make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]));
         }
     }
     // ---------------------------------------------------------------------- write-out: all ten warps
@@ -317,20 +398,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     __syncthreads();
     STAMP(6, threadIdx.x == 192);
     {
-        const float* tile = reinterpret_cast<const float*>(smem);
+        const uint32_t tile = smem_u32(smem) + lane * 16;          // this lane's four columns of row 0
         const int64_t n = (int64_t)n0 + lane * 4;
         const int nvalid = (int)max((int64_t)0, min((int64_t)4, p.N - n));
         constexpr int RPI = 4;
         if (partial != nullptr) {
             float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
             const bool vec = (p.N % 4 == 0);
+            if (vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N) {       // interior tile: branch-free
+                float* cp = dst + ((int64_t)m0 + warp * RPI) * p.N + n;
+                uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
+#pragma unroll 1
+                for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
+                    float4 a4[RPI];
+#pragma unroll
+                    for (int i = 0; i < RPI; ++i) a4[i] = lds128(ts + i * (EPI_LD * 4));
+#pragma unroll
+                    for (int i = 0; i < RPI; ++i) *reinterpret_cast<float4*>(cp + i * p.N) = a4[i];
+                    ts += (THREADS / 32) * RPI * (EPI_LD * 4);
+                    cp += (THREADS / 32) * RPI * p.N;
+                }
+            } else
             for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
 #pragma unroll
                 for (int i = 0; i < RPI; ++i) {
                     const int r = r0 + i;
                     const int64_t m = (int64_t)m0 + r;
                     if (r >= BM || m >= p.M || nvalid == 0) continue;
-                    const float4 a4 = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+                    const float4 a4 = lds128(tile + r * (EPI_LD * 4));
                     float* cp = dst + m * p.N + n;
                     if (vec && nvalid == 4) {
                         *reinterpret_cast<float4*>(cp) = a4;
@@ -345,6 +440,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         } else {
             const bool has_drop = p.drop_p > 0.f;
             const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
+            const bool al1 = !p.res1 || ((p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0));
+            const bool al2 = !p.res2 || ((p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0));
+            const bool alb = !p.bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+            if (p.c_vec && al1 && al2 && alb && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N && !(p.res2 && !p.res1)) {
+                const bool act = p.act == 1;
+                if (p.res2) writeout_interior_dispatch<2>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+                else if (p.res1) writeout_interior_dispatch<1>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+                else writeout_interior_dispatch<0>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+            } else {
             float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
             if (p.bias) {
                 if (nvalid > 0) bv.x = __ldg(p.bias + n);
@@ -364,7 +468,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     ok[i] = r < BM && m < p.M && nvalid > 0;
                     a4[i] = q1[i] = q2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (!ok[i]) continue;
-                    a4[i] = *reinterpret_cast<const float4*>(tile + r * EPI_LD + lane * 4);
+                    a4[i] = lds128(tile + r * (EPI_LD * 4));
                     if (p.res1) {
                         const float* rp = p.res1 + m * p.ldr1 + n;
                         if (vec_res1) q1[i] = __ldg(reinterpret_cast<const float4*>(rp));
@@ -412,6 +516,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                     }
                 }
             }
+            }   // general (edge / unaligned) path
         }
     }
     STAMP(7, threadIdx.x == 192);

@@ -8,7 +8,7 @@ h = ctypes.CDLL(_lib.LIB_PATH)
 fn = h.grappa_gemm; fn.restype = ctypes.c_int; fn.argtypes = _lib.PROTOTYPES["grappa_gemm"][1]
 tl = h.grappa_debug_timeline; tl.restype = ctypes.c_int
 dev = "cuda"
-for (M, N, K) in [(18944, 128, 32), (18944, 128, 256), (18944, 128, 1024), (128, 128, 256)]:
+for (M, N, K) in [(1536, 256, 256), (6080, 256, 256), (12160, 512, 512), (128, 128, 256), (128, 128, 32)]:
     A = torch.randn(M, K, device=dev); B = torch.randn(N, K, device=dev); C = torch.empty(M, N, device=dev)
     for it in range(3):
         rc = fn(0, M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, None, 0, None, 0, 0.0, 0, None, 1, None, 0, None)
