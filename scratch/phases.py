@@ -71,3 +71,18 @@ except Exception as e: print("full parallel failed:", str(e)[:80])
 try:
     timed("full fwd+loss+bwd (serial writers)", full_serial)
 except Exception as e: print("full serial failed:", str(e)[:80])
+hleaf = g.nodes["n1"].data["h"].detach().clone().requires_grad_(True)
+def writer_fb(w, lvl):
+    def f():
+        g.nodes["n1"].data["h"] = hleaf
+        w(g, plan)
+        d = g.nodes[lvl].data
+        outs = [d[k] for k in ("k", "eq") if k in d and d[k].requires_grad]
+        torch.autograd.backward(outs, [torch.ones_like(o) for o in outs])
+        ops.join_side_work(dev)
+    return f
+for name, w, lvl in (("bond", model.parameter_writer.bond_writer, "n2"), ("angle", model.parameter_writer.angle_writer, "n3"), ("proper", model.parameter_writer.proper_writer, "n4"), ("improper", model.parameter_writer.improper_writer, "n4_improper")):
+    try:
+        timed(f"  {name} writer fwd+bwd alone", writer_fb(w, lvl))
+    except Exception as e:
+        print(name, "failed", str(e)[:100])
