@@ -56,6 +56,7 @@ _WRITER_STREAMS = {}
 
 
 def _writer_streams(device):
+    device = ops.norm_device(device)
     st = _WRITER_STREAMS.get(device)
     if st is None:
         st = [torch.cuda.Stream(device=device) for _ in range(4)]

@@ -26,7 +26,16 @@ _SIDE_STREAMS = {}
 _DEFERRED = []
 
 
+def norm_device(device) -> torch.device:
+    """'cuda' and 'cuda:0' must name the same per-device state (streams, workspaces): always carry the index."""
+    device = torch.device(device)
+    if device.type == "cuda" and device.index is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    return device
+
+
 def _side_stream(device):
+    device = norm_device(device)
     st = _SIDE_STREAMS.get(device)
     if st is None:
         st = torch.cuda.Stream(device=device)
@@ -36,6 +45,7 @@ def _side_stream(device):
 
 def join_side_work(device):
     """Make the current stream wait for all side-stream gradient work; called once after backward."""
+    device = norm_device(device)
     st = _SIDE_STREAMS.get(device)
     if st is not None:
         torch.cuda.current_stream(device).wait_stream(st)
@@ -114,6 +124,7 @@ WORKSPACE_FLOATS = 8 * 1024 * 1024       # 32 MB split-K scratch per device, all
 
 def _workspace(device):
     """Split-K scratch, one per (device, stream): GEMMs of the four parameter writers run on parallel streams."""
+    device = norm_device(device)
     key = (device, torch.cuda.current_stream(device).cuda_stream)
     ws = _WORKSPACE.get(key)
     if ws is None:

@@ -57,8 +57,8 @@ class TrainStep:
     def __init__(self, model, device, lr: float = 1e-5, weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8,
                  energy_weight: float = 1.0, gradient_weight: float = 0.8, proper_regularisation: float = 1.0,
                  improper_regularisation: float = 1.0, world_size: int = 1, use_cuda_graph: bool = True,
-                 process_group=None):
-        self.device = torch.device(device)
+                 process_group=None, overlap_comm: Optional[bool] = None):
+        self.device = ops.norm_device(device)
         self.model = model.to(self.device).train()
         self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
         self.flat = FlatParameters(self.model, self.device)
@@ -68,6 +68,13 @@ class TrainStep:
         self.pg = process_group
         self.use_cuda_graph = use_cuda_graph
         self.t = 0
+        # Two gradient buckets in backward order: the four writers' parameters (second half of the flat
+        # buffer) are complete once the backward pass reaches the atom embedding, so their all-reduce runs while the
+        # GNN backward is still computing; the GNN bucket follows.  Needs the backward split at the embedding.
+        self.overlap_comm = (world_size > 1) if overlap_comm is None else overlap_comm
+        first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
+        self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
+        assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
         self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
         self._static: Dict[tuple, dict] = {}
         # warm-up and capture both run on this side stream (the whole-network capture recipe of torch.cuda.graphs:
@@ -91,6 +98,96 @@ class TrainStep:
             ops.GRAD_SINK = None
             ops.DropoutSeeds.dev = None
         return loss.detach()
+
+    # ---- the same in two phases, split where the backward pass reaches the atom embedding ------------------------------
+    def _phase_a(self, g):
+        """GNN forward, writers + energy + loss forward, backward down to the embedding (all writer gradients done)."""
+        ops.GRAD_SINK = self.flat.sink
+        ops.DropoutSeeds.dev = self.seed_dev
+        try:
+            plan = get_plan(g)
+            g = self.model.gnn(g, plan)
+            h = g.nodes["n1"].data["h"]
+            leaf = h.detach().requires_grad_(True)
+            g.nodes["n1"].data["h"] = leaf
+            g = self.energy(self.model.parameter_writer(g, plan))
+            gd, n1 = g.nodes["g"].data, g.nodes["n1"].data
+            loss = ops.MolwiseLossFn.apply(gd["energy"], n1["gradient"], g.nodes["n4"].data["k"], g.nodes["n4_improper"].data["k"],
+                                           gd["energy_ref"], n1["gradient_ref"], gd.get("is_dummy"), plan, self.weights)
+            loss.backward()
+            # the backward pass ends on the four writer streams (nothing downstream consumes them in this phase):
+            # join them explicitly, which is also what closes the forked branches under graph capture
+            from . import model as _model
+            if _model.PARALLEL_WRITERS:
+                cur = torch.cuda.current_stream(self.device)
+                for wst in _model._writer_streams(self.device):
+                    cur.wait_stream(wst)
+            ops.join_side_work(self.device)
+        finally:
+            ops.GRAD_SINK = None
+            ops.DropoutSeeds.dev = None
+        return loss.detach(), h, leaf
+
+    def _phase_b(self, h, leaf):
+        """GNN backward from the embedding gradient."""
+        ops.GRAD_SINK = self.flat.sink
+        ops.DropoutSeeds.dev = self.seed_dev
+        try:
+            h.backward(leaf.grad)
+            ops.join_side_work(self.device)
+            self.seed_dev.add_(1)
+        finally:
+            ops.GRAD_SINK = None
+            ops.DropoutSeeds.dev = None
+
+    def _run_split(self, st, g, between):
+        """Phase A, `between()` (the first bucket's all-reduce), phase B; eager during warm-up, two graphs afterwards."""
+        if not self.use_cuda_graph:
+            loss, h, leaf = self._phase_a(g)
+            between()
+            self._phase_b(h, leaf)
+            return loss
+        if st.get("graph_a") is None:
+            cur = torch.cuda.current_stream(self.device)
+            if st["warm"] < 3:
+                st["warm"] += 1
+                self._side.wait_stream(cur)
+                with torch.cuda.stream(self._side):
+                    loss, h, leaf = self._phase_a(g)
+                    self._phase_b(h, leaf)
+                cur.wait_stream(self._side)
+                between()
+                return loss
+            torch.cuda.synchronize(self.device)
+            ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(ga, stream=self._side):
+                st["loss"], h, leaf = self._phase_a(g)
+            with torch.cuda.graph(gb, stream=self._side, pool=ga.pool()):
+                self._phase_b(h, leaf)
+            st["graph_a"], st["graph_b"] = ga, gb
+        st["graph_a"].replay()
+        between()
+        st["graph_b"].replay()
+        return st["loss"]
+
+    def _step_overlapped(self, st) -> torch.Tensor:
+        g = st["batch"].graph
+        works = []
+        dist = torch.distributed
+        multi = self.world_size > 1
+
+        def first_bucket():
+            if multi and self.bucket_split < self.flat.numel:
+                works.append(dist.all_reduce(self.flat.grads[self.bucket_split:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+
+        loss = self._run_split(st, g, first_bucket)
+        if multi and self.bucket_split > 0:
+            works.append(dist.all_reduce(self.flat.grads[:self.bucket_split], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+        for w in works:
+            w.wait()
+        self._grad_scale = 1.0 / self.world_size
+        self.optimizer_step()
+        return loss
 
     def _state_for(self, packed: PackedBatch):
         st = self._static.get(packed.signature)
@@ -140,12 +237,19 @@ class TrainStep:
         spec = store.prepare(mol_ids, conf_strategy, generator)
         st = self._state_for(spec)
         store.collate_into(spec, st["batch"])
+        if self.overlap_comm:
+            return self._step_overlapped(st)
         loss = self.compute_gradients(spec, load=False)
         self.all_reduce_gradients()
         self.optimizer_step()
         return loss
 
     def step(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
+        if self.overlap_comm:
+            st = self._state_for(packed)
+            if load:
+                st["batch"].load(packed)
+            return self._step_overlapped(st)
         loss = self.compute_gradients(packed, load=load)
         self.all_reduce_gradients()
         self.optimizer_step()

@@ -244,3 +244,26 @@ def test_python_default_config_ungated_torsions():
     assert gd.nodes["n4_improper"].data["k"].shape == (48, 3)
     assert float(gd.nodes["n4_improper"].data["k"][:, [0, 2]].abs().max()) == 0.0
     assert_params_close(graph_params(gd), p_ref, "python-default config")
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_split_backward_for_bucketed_allreduce_is_bit_identical(use_graph):
+    """TrainStep(overlap_comm=True) splits the backward pass at the atom embedding so that the writers' gradient bucket can
+    be all-reduced while the GNN backward runs.  With one rank the exchange is a no-op and the updated
+    weights must equal the single-pass step bit for bit, eagerly and through the two captured graphs."""
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.train_step import TrainStep
+    packed = PackedBatch(batch([S.trimer_molecule(seed=s, n_confs=5) for s in range(4)]))
+    outs = []
+    from grappa_b200 import ops
+    for overlap in (False, True):
+        model, _ = build_model(train=True)
+        ops.DropoutSeeds.manual_seed(1234)           # dropout stays ON: both runs must draw the same masks
+        ts = TrainStep(model, DEV, use_cuda_graph=use_graph, overlap_comm=overlap)
+        assert 0 < ts.bucket_split < ts.flat.numel
+        losses = [float(ts.step(packed)) for _ in range(5)]        # with graphs: 3 eager warm-ups, capture, replay
+        torch.cuda.synchronize()
+        outs.append((losses, ts.flat.params.clone(), ts.flat.grads.clone()))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][2], outs[1][2])
+    assert torch.equal(outs[0][1], outs[1][1])
