@@ -27,6 +27,22 @@ from .plan import get_plan
 _UNUSED = ("grappa_transformer.norm.",)
 
 
+class _BucketBoundary(torch.autograd.Function):
+    """Identity on the atom embedding between the GNN and the four writers.  Its backward runs once all writers'
+    contributions to dL/dh have been accumulated, i.e. after every writer gradient kernel has been issued: the point
+    where the writers' gradient bucket can go on the wire."""
+
+    @staticmethod
+    def forward(ctx, h, step):
+        ctx.step = step
+        return h.view_as(h)
+
+    @staticmethod
+    def backward(ctx, grad):
+        ctx.step._reduce_writer_bucket()
+        return grad, None
+
+
 class FlatParameters:
     def __init__(self, model: torch.nn.Module, device):
         self.named = [(n, p) for n, p in model.named_parameters() if p.requires_grad and not any(u in n for u in _UNUSED)]
@@ -69,9 +85,21 @@ class TrainStep:
         self.use_cuda_graph = use_cuda_graph
         self.t = 0
         # Two gradient buckets in backward order: the four writers' parameters (second half of the flat
-        # buffer) are complete once the backward pass reaches the atom embedding, so their all-reduce runs while the
-        # GNN backward is still computing; the GNN bucket follows.  Needs the backward split at the embedding.
-        self.overlap_comm = (world_size > 1) if overlap_comm is None else overlap_comm
+        # buffer) are complete once the backward pass reaches the atom embedding, so their all-reduce is issued from
+        # an autograd boundary node at that point, on a communication stream, and runs while the GNN backward is still
+        # computing; the GNN bucket follows after backward.  Under CUDA-graph capture the NCCL launches become nodes of
+        # the step's graph (a parallel branch).
+        # STATUS (round 1): the stream choreography is verified on one GPU with a stand-in exchange
+        # (tests/test_gpu_model.py::test_bucketed_gradient_exchange_choreography), but with real NCCL collectives the
+        # 2-GPU run hung (twice, issued from the autograd thread and from the calling thread), so it is OFF by default and
+        # refused for world_size > 1 until that is understood; the default is one all-reduce after backward (measured
+        # exposed cost: 0.19 ms at N = 2, 0.38 ms at N = 8 of a 5.2 ms step).
+        self.overlap_comm = bool(overlap_comm)
+        if self.overlap_comm and world_size > 1:
+            raise NotImplementedError("overlap_comm with NCCL hung on 2 x B200 in round 1; use the default single all-reduce")
+        self._comm_stream = torch.cuda.Stream(device=self.device)
+        self._works = []
+        self._reduce_fn = None            # test hook: replaces the NCCL all-reduce of one bucket
         first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
         self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
         assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
@@ -86,108 +114,60 @@ class TrainStep:
         ops.GRAD_SINK = self.flat.sink
         ops.DropoutSeeds.dev = self.seed_dev
         try:
-            g = self.energy(self.model(g))
+            if self.overlap_comm:
+                plan = get_plan(g)
+                g = self.model.gnn(g, plan)
+                g.nodes["n1"].data["h"] = _BucketBoundary.apply(g.nodes["n1"].data["h"], self)
+                g = self.energy(self.model.parameter_writer(g, plan))
+            else:
+                g = self.energy(self.model(g))
             plan = get_plan(g)
             gd, n1 = g.nodes["g"].data, g.nodes["n1"].data
             loss = ops.MolwiseLossFn.apply(gd["energy"], n1["gradient"], g.nodes["n4"].data["k"], g.nodes["n4_improper"].data["k"],
                                            gd["energy_ref"], n1["gradient_ref"], gd.get("is_dummy"), plan, self.weights)
             loss.backward()
             ops.join_side_work(self.device)
+            if self.overlap_comm:
+                # Both collectives are ISSUED here, by the calling thread (NCCL calls from the autograd worker thread
+                # hung); what makes the first one overlap the GNN backward is its dependency: the communication
+                # stream only waits for the writers' work as it stood when the boundary node ran.
+                with torch.cuda.stream(self._comm_stream):
+                    self._reduce_bucket(self.flat.grads[self.bucket_split:])      # writers' bucket
+                self._reduce_bucket(self.flat.grads[:self.bucket_split])          # GNN bucket, after the whole backward
+                cur = torch.cuda.current_stream(self.device)
+                for w in self._works:
+                    if w is not None:
+                        w.wait()
+                self._works.clear()
+                cur.wait_stream(self._comm_stream)
             self.seed_dev.add_(1)
         finally:
             ops.GRAD_SINK = None
             ops.DropoutSeeds.dev = None
         return loss.detach()
 
-    # ---- the same in two phases, split where the backward pass reaches the atom embedding ------------------------------
-    def _phase_a(self, g):
-        """GNN forward, writers + energy + loss forward, backward down to the embedding (all writer gradients done)."""
-        ops.GRAD_SINK = self.flat.sink
-        ops.DropoutSeeds.dev = self.seed_dev
-        try:
-            plan = get_plan(g)
-            g = self.model.gnn(g, plan)
-            h = g.nodes["n1"].data["h"]
-            leaf = h.detach().requires_grad_(True)
-            g.nodes["n1"].data["h"] = leaf
-            g = self.energy(self.model.parameter_writer(g, plan))
-            gd, n1 = g.nodes["g"].data, g.nodes["n1"].data
-            loss = ops.MolwiseLossFn.apply(gd["energy"], n1["gradient"], g.nodes["n4"].data["k"], g.nodes["n4_improper"].data["k"],
-                                           gd["energy_ref"], n1["gradient_ref"], gd.get("is_dummy"), plan, self.weights)
-            loss.backward()
-            # the backward pass ends on the four writer streams (nothing downstream consumes them in this phase):
-            # join them explicitly, which is also what closes the forked branches under graph capture
-            from . import model as _model
-            if _model.PARALLEL_WRITERS:
-                cur = torch.cuda.current_stream(self.device)
-                for wst in _model._writer_streams(self.device):
-                    cur.wait_stream(wst)
-            ops.join_side_work(self.device)
-        finally:
-            ops.GRAD_SINK = None
-            ops.DropoutSeeds.dev = None
-        return loss.detach(), h, leaf
+    def _reduce_bucket(self, view: torch.Tensor):
+        if view.numel() == 0:
+            return
+        if self._reduce_fn is not None:
+            self._reduce_fn(view)
+        elif self.world_size > 1:
+            dist = torch.distributed
+            self._works.append(dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
 
-    def _phase_b(self, h, leaf):
-        """GNN backward from the embedding gradient."""
-        ops.GRAD_SINK = self.flat.sink
-        ops.DropoutSeeds.dev = self.seed_dev
-        try:
-            h.backward(leaf.grad)
-            ops.join_side_work(self.device)
-            self.seed_dev.add_(1)
-        finally:
-            ops.GRAD_SINK = None
-            ops.DropoutSeeds.dev = None
-
-    def _run_split(self, st, g, between):
-        """Phase A, `between()` (the first bucket's all-reduce), phase B; eager during warm-up, two graphs afterwards."""
-        if not self.use_cuda_graph:
-            loss, h, leaf = self._phase_a(g)
-            between()
-            self._phase_b(h, leaf)
-            return loss
-        if st.get("graph_a") is None:
-            cur = torch.cuda.current_stream(self.device)
-            if st["warm"] < 3:
-                st["warm"] += 1
-                self._side.wait_stream(cur)
-                with torch.cuda.stream(self._side):
-                    loss, h, leaf = self._phase_a(g)
-                    self._phase_b(h, leaf)
-                cur.wait_stream(self._side)
-                between()
-                return loss
-            torch.cuda.synchronize(self.device)
-            ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-            with torch.cuda.graph(ga, stream=self._side):
-                st["loss"], h, leaf = self._phase_a(g)
-            with torch.cuda.graph(gb, stream=self._side, pool=ga.pool()):
-                self._phase_b(h, leaf)
-            st["graph_a"], st["graph_b"] = ga, gb
-        st["graph_a"].replay()
-        between()
-        st["graph_b"].replay()
-        return st["loss"]
-
-    def _step_overlapped(self, st) -> torch.Tensor:
-        g = st["batch"].graph
-        works = []
-        dist = torch.distributed
-        multi = self.world_size > 1
-
-        def first_bucket():
-            if multi and self.bucket_split < self.flat.numel:
-                works.append(dist.all_reduce(self.flat.grads[self.bucket_split:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
-
-        loss = self._run_split(st, g, first_bucket)
-        if multi and self.bucket_split > 0:
-            works.append(dist.all_reduce(self.flat.grads[:self.bucket_split], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
-        for w in works:
-            w.wait()
-        self._grad_scale = 1.0 / self.world_size
-        self.optimizer_step()
-        return loss
+    def _reduce_writer_bucket(self):
+        """Called from the boundary node's backward: every writer gradient kernel has been issued (on the writer streams
+        and the side stream); the communication stream picks up exactly these dependencies (event waits only)."""
+        from . import model as _model
+        cur = torch.cuda.current_stream(self.device)
+        comm = self._comm_stream
+        comm.wait_stream(cur)
+        if _model.PARALLEL_WRITERS:
+            for wst in _model._writer_streams(self.device):
+                comm.wait_stream(wst)
+        side = ops._SIDE_STREAMS.get(self.device)
+        if side is not None:
+            comm.wait_stream(side)
 
     def _state_for(self, packed: PackedBatch):
         st = self._static.get(packed.signature)
@@ -222,6 +202,9 @@ class TrainStep:
         return st["loss"]
 
     def all_reduce_gradients(self):
+        if self.overlap_comm:            # already exchanged inside compute_gradients (two buckets)
+            self._grad_scale = 1.0 / self.world_size
+            return
         self._grad_scale = all_reduce_sum_(self.flat.grads, self.world_size, self.pg)
 
     def optimizer_step(self):
@@ -237,19 +220,12 @@ class TrainStep:
         spec = store.prepare(mol_ids, conf_strategy, generator)
         st = self._state_for(spec)
         store.collate_into(spec, st["batch"])
-        if self.overlap_comm:
-            return self._step_overlapped(st)
         loss = self.compute_gradients(spec, load=False)
         self.all_reduce_gradients()
         self.optimizer_step()
         return loss
 
     def step(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
-        if self.overlap_comm:
-            st = self._state_for(packed)
-            if load:
-                st["batch"].load(packed)
-            return self._step_overlapped(st)
         loss = self.compute_gradients(packed, load=load)
         self.all_reduce_gradients()
         self.optimizer_step()

@@ -247,23 +247,34 @@ def test_python_default_config_ungated_torsions():
 
 
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_split_backward_for_bucketed_allreduce_is_bit_identical(use_graph):
-    """TrainStep(overlap_comm=True) splits the backward pass at the atom embedding so that the writers' gradient bucket can
-    be all-reduced while the GNN backward runs.  With one rank the exchange is a no-op and the updated
-    weights must equal the single-pass step bit for bit, eagerly and through the two captured graphs."""
+def test_bucketed_gradient_exchange_choreography(use_graph):
+    """TrainStep(overlap_comm=True) issues the writers' gradient bucket from an autograd boundary node at the atom
+    embedding (on a communication stream, while the GNN backward runs) and the GNN bucket after backward.
+    One GPU cannot run NCCL against a peer, so the exchange is replaced by a stand-in that doubles the bucket in place
+    (what a 2-rank sum of identical gradients would give): every gradient must come out exactly doubled, every element
+    exactly once, eagerly and through the captured graph, and with the exchange disabled the step is unchanged."""
     from grappa_b200.batching import PackedBatch
     from grappa_b200.train_step import TrainStep
     packed = PackedBatch(batch([S.trimer_molecule(seed=s, n_confs=5) for s in range(4)]))
-    outs = []
-    from grappa_b200 import ops
-    for overlap in (False, True):
+    outs = {}
+    for mode in ("plain", "overlap_noop", "overlap_double"):
         model, _ = build_model(train=True)
-        ops.DropoutSeeds.manual_seed(1234)           # dropout stays ON: both runs must draw the same masks
-        ts = TrainStep(model, DEV, use_cuda_graph=use_graph, overlap_comm=overlap)
+        ops.DropoutSeeds.manual_seed(1234)           # dropout stays ON: all runs must draw the same masks
+        ts = TrainStep(model, DEV, use_cuda_graph=use_graph, overlap_comm=(mode != "plain"))
         assert 0 < ts.bucket_split < ts.flat.numel
-        losses = [float(ts.step(packed)) for _ in range(5)]        # with graphs: 3 eager warm-ups, capture, replay
+        calls = []
+        if mode == "overlap_double":
+            def fake(view):
+                calls.append((view.data_ptr(), view.numel()))
+                view.mul_(2.0)
+            ts._reduce_fn = fake
+        for _ in range(5):                            # with graphs: 3 eager warm-ups, capture, replay
+            loss = ts.compute_gradients(packed)
         torch.cuda.synchronize()
-        outs.append((losses, ts.flat.params.clone(), ts.flat.grads.clone()))
-    assert outs[0][0] == outs[1][0]
-    assert torch.equal(outs[0][2], outs[1][2])
-    assert torch.equal(outs[0][1], outs[1][1])
+        outs[mode] = (float(loss), ts.flat.grads.clone())
+        if mode == "overlap_double":
+            assert len(calls) >= 2 and sum(n for _, n in calls[:2]) == ts.flat.numel     # two buckets tile the buffer
+            assert calls[0][1] == ts.flat.numel - ts.bucket_split                          # writers first
+    assert outs["plain"][0] == outs["overlap_noop"][0] == outs["overlap_double"][0]
+    assert torch.equal(outs["plain"][1], outs["overlap_noop"][1])
+    assert torch.equal(outs["plain"][1] * 2.0, outs["overlap_double"][1])
