@@ -47,6 +47,10 @@ PROTOTYPES = {
                               P, P, P, P, P, P, P]),
     "grappa_csr_build": (I, [I64, I64, P, P, P]),
     "grappa_enumerate_tuples": (I, [I64, P, I64, P, P, P]),
+    "grappa_pe_table_fwd": (I, [I64, I, I, P, I64, P, P]),
+    "grappa_pe_table_bwd": (I, [I64, I, I, P, P, I64, P]),
+    "grappa_row_gather_fwd": (I, [I64, I, P, I64, P, P, I64, P]),
+    "grappa_row_gather_bwd": (I, [I64, I, P, I64, P, P, P, I64, P]),
     "grappa_collate_int": (I, [I64, P, P, P, P, P]),
     "grappa_collate_float": (I, [I64, P, P, P, P, P]),
     "grappa_molwise_loss": (I, [I64, I64, P, P, P, P, P, P, P, P, P, I, P, I, F, F, F, F, P, P, P, P, P, P, P, P]),

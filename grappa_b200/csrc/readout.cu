@@ -55,6 +55,91 @@ __global__ void __launch_bounds__(256) tuple_gather_bwd_kernel(int64_t N, int F,
     }
 }
 
+
+// ------------------------------------------------------------------------------- token de-duplication (row tables) ---
+// The first LayerNorm and the QKV projection of a writer's transformer see tokens whose content depends only on
+// (atom, positional-encoding value): at most 2 N distinct rows for T * n_seq tokens (4.75x fewer for proper torsions of
+// the benchmark molecules, 5.3x for a protein).  They are therefore computed once per table row and gathered per token.
+
+// U[2a + pe, c] = c < F ? P[a, c] : pe          (pe in {0, 1}; W = padded width, multiple of 4)
+__global__ void pe_table_fwd_kernel(int64_t N, int F, int W, const float* __restrict__ P, int64_t ldp, float* __restrict__ U) {
+    const int W4 = W / 4;
+    const int64_t total = 2 * N * W4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / W4;
+        const int c = (int)(i % W4) * 4;
+        const float pv = (float)(r & 1);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < F) v = __ldg(reinterpret_cast<const float4*>(P + (r >> 1) * ldp + c));
+        if (c + 0 >= F) v.x = pv;
+        if (c + 1 >= F) v.y = pv;
+        if (c + 2 >= F) v.z = pv;
+        if (c + 3 >= F) v.w = pv;
+        reinterpret_cast<float4*>(U)[i] = v;
+    }
+}
+
+// dP[a, c] = c < F ? dU[2a, c] + dU[2a + 1, c] : 0     (columns up to lddp are written)
+__global__ void pe_table_bwd_kernel(int64_t N, int F, int W, const float* __restrict__ dU, float* __restrict__ dP, int64_t lddp) {
+    const int L4 = (int)(lddp / 4);
+    const int64_t total = N * L4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t a = i / L4;
+        const int c = (int)(i % L4) * 4;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < W) {
+            const float4 u = __ldg(reinterpret_cast<const float4*>(dU + (2 * a) * W + c));
+            const float4 v = __ldg(reinterpret_cast<const float4*>(dU + (2 * a + 1) * W + c));
+            s = make_float4(u.x + v.x, u.y + v.y, u.z + v.z, u.w + v.w);
+        }
+        if (c + 0 >= F) s.x = 0.f;
+        if (c + 1 >= F) s.y = 0.f;
+        if (c + 2 >= F) s.z = 0.f;
+        if (c + 3 >= F) s.w = 0.f;
+        *reinterpret_cast<float4*>(dP + a * lddp + c) = s;
+    }
+}
+
+// X[r, :] = Tab[idx[r], :]
+__global__ void row_gather_fwd_kernel(int64_t rows, int D, const float* __restrict__ Tab, int64_t ldt,
+                                      const int32_t* __restrict__ idx, float* __restrict__ X, int64_t ldx) {
+    const int D4 = D / 4;
+    const int64_t total = rows * D4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / D4;
+        const int c = (int)(i % D4) * 4;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(Tab + (int64_t)__ldg(idx + r) * ldt + c));
+        *reinterpret_cast<float4*>(X + r * ldx + c) = v;
+    }
+}
+
+// one warp per (table row, 128-column slab): dTab[j, :] = sum over the rows listed for j of dX[row, :], in list order
+__global__ void __launch_bounds__(256) row_gather_bwd_kernel(int64_t R, int D, const float* __restrict__ dX, int64_t ldx,
+                                                             const int32_t* __restrict__ ptr, const int32_t* __restrict__ tok,
+                                                             float* __restrict__ dTab, int64_t ldt) {
+    const int slabs = (D + 127) / 128;
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= R * slabs) return;
+    const int64_t j = w / slabs;
+    const int c = (int)(w % slabs) * 128 + lane * 4;
+    if (c >= D) return;
+    const int q0 = __ldg(ptr + j), q1 = __ldg(ptr + j + 1);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int q = q0;
+    for (; q + 1 < q1; q += 2) {                   // two independent loads in flight, added in list order
+        const float4 u = __ldg(reinterpret_cast<const float4*>(dX + (int64_t)__ldg(tok + q) * ldx + c));
+        const float4 v = __ldg(reinterpret_cast<const float4*>(dX + (int64_t)__ldg(tok + q + 1) * ldx + c));
+        s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w;
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    if (q < q1) {
+        const float4 u = __ldg(reinterpret_cast<const float4*>(dX + (int64_t)__ldg(tok + q) * ldx + c));
+        s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w;
+    }
+    *reinterpret_cast<float4*>(dTab + j * ldt + c) = s;
+}
+
 // ------------------------------------------------------------------------------------------ tuple attention ---
 
 __device__ __forceinline__ float sum8(float v) {
@@ -352,6 +437,45 @@ extern "C" int grappa_tuple_gather_bwd(int64_t N, int F, int W, const float* dX,
     if (N == 0) return 0;
     GRAPPA_CHECK_ARG(inc_ptr && inc_tok && dA, "null pointer");
     tuple_gather_bwd_kernel<<<(unsigned)ceil_div(N * 32, 256), 256, 0, (cudaStream_t)stream>>>(N, F, W, dX, inc_ptr, inc_tok, dA, ldda);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_pe_table_fwd(int64_t N, int F, int W, const float* P, int64_t ldp, float* U, void* stream) {
+    GRAPPA_CHECK_ARG(N >= 0 && F > 0 && F <= W && W % 4 == 0 && ldp % 4 == 0 && ldp >= ((F + 3) / 4) * 4, "bad sizes");
+    if (N == 0) return 0;
+    GRAPPA_CHECK_ARG(P && U, "null pointer");
+    pe_table_fwd_kernel<<<grid_for(2 * N * (W / 4)), 256, 0, (cudaStream_t)stream>>>(N, F, W, P, ldp, U);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_pe_table_bwd(int64_t N, int F, int W, const float* dU, float* dP, int64_t lddp, void* stream) {
+    GRAPPA_CHECK_ARG(N >= 0 && F > 0 && F <= W && W % 4 == 0 && lddp % 4 == 0 && lddp >= W, "bad sizes");
+    if (N == 0) return 0;
+    GRAPPA_CHECK_ARG(dU && dP, "null pointer");
+    pe_table_bwd_kernel<<<grid_for(N * (lddp / 4)), 256, 0, (cudaStream_t)stream>>>(N, F, W, dU, dP, lddp);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_row_gather_fwd(int64_t rows, int D, const float* table, int64_t ldt, const int32_t* idx, float* X,
+                                     int64_t ldx, void* stream) {
+    GRAPPA_CHECK_ARG(rows >= 0 && D > 0 && D % 4 == 0 && ldt % 4 == 0 && ldx % 4 == 0 && ldt >= D && ldx >= D, "bad sizes");
+    if (rows == 0) return 0;
+    GRAPPA_CHECK_ARG(table && idx && X, "null pointer");
+    row_gather_fwd_kernel<<<grid_for(rows * (D / 4)), 256, 0, (cudaStream_t)stream>>>(rows, D, table, ldt, idx, X, ldx);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_row_gather_bwd(int64_t table_rows, int D, const float* dX, int64_t ldx, const int32_t* ptr,
+                                     const int32_t* tok, float* dTable, int64_t ldt, void* stream) {
+    GRAPPA_CHECK_ARG(table_rows >= 0 && D > 0 && D % 4 == 0 && ldt % 4 == 0 && ldx % 4 == 0 && ldt >= D && ldx >= D, "bad sizes");
+    if (table_rows == 0) return 0;
+    GRAPPA_CHECK_ARG(dX && ptr && tok && dTable, "null pointer");
+    const int64_t warps = table_rows * ((D + 127) / 128);
+    row_gather_bwd_kernel<<<(unsigned)ceil_div(warps * 32, 256), 256, 0, (cudaStream_t)stream>>>(table_rows, D, dX, ldx, ptr, tok, dTable, ldt);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }

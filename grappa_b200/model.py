@@ -22,7 +22,7 @@ import torch
 from torch import nn
 
 from . import ops
-from .plan import get_plan
+from .plan import PE_PATTERN, get_plan
 
 MAX_ELEMENT = 53            # constants.py:38
 CHARGE_ENCODING_DIM = 16    # graph_attention.py:53
@@ -53,6 +53,12 @@ DEFAULT_CONFIG = dict(   # configs/model/default.yaml
 
 PARALLEL_WRITERS = True
 _WRITER_STREAMS = {}
+
+
+# Token de-duplication (see csrc/readout.cu): the first LayerNorm + QKV projection of a writer's transformer run once per
+# distinct (atom, pe) row instead of once per token whenever there are at least DEDUP_RATIO times more tokens than rows.
+DEDUP_TOKENS = True
+DEDUP_RATIO = 1.5
 
 
 def _writer_streams(device):
@@ -259,9 +265,17 @@ class DottedAttWithMLP(nn.Module):
         """network_utils.py:113-136 on tuple-major tokens (T*n_seq, n_feats).
         outer_residual: the transformer input X; when given, X * (col < outer_feats ? 2 : 1) is added to the block
         output in the last GEMM epilogue (perm_equiv_transformer.py:165 and :75-77)."""
-        p = self.dropout.p if self.training else 0.0
+        x, qkv = self.pre(x)
+        return self.post(x, qkv, T, n_seq, outer_residual, outer_feats)
+
+    def pre(self, x):
+        """norm1 + the QKV projection (network_utils.py:119-123): row-wise, so callers may apply it to the table of
+        distinct token contents instead of the tokens."""
         x = ops.layer_norm(x, self.norm1.weight, self.norm1.bias)
-        qkv = ops.linear(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
+        return x, ops.linear(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
+
+    def post(self, x, qkv, T, n_seq, outer_residual=None, outer_feats=0):
+        p = self.dropout.p if self.training else 0.0
         o = ops.tuple_attention(qkv, T, n_seq, self.num_heads)
         x = ops.linear(o, self.attn.out_proj.weight, self.attn.out_proj.bias, res1=x, drop_p=p)
         x = ops.layer_norm(x, self.norm2.weight, self.norm2.bias)
@@ -361,15 +375,50 @@ class SymmetrisedTransformer(nn.Module):
         gt = self.grappa_transformer
         n_seq, T = gt.n_seq, plan.T[level]
         pe = gt.positional_encoding
-        x_in = ops.tuple_gather(atom_feats, plan, level, n_seq, self.n_feats, self.trafo_out_feats,
-                                None if pe is None else pe.reshape(-1).contiguous())
-        x = x_in
         n_blocks = len(gt.transformer)
-        for i, blk in enumerate(gt.transformer):
+        names = self._dedup_tables(plan, level, atom_feats.shape[0], T * n_seq)
+        if names is not None:
+            # distinct token contents: the projected atom rows themselves (no PE column) or the (atom, pe) table
+            table = atom_feats if pe is None else ops.pe_table(atom_feats, self.n_feats, self.trafo_out_feats)
+            x1_tab, qkv_tab = gt.transformer[0].pre(table)
+            rows = T * n_seq
+            x_in = ops.row_gather(table, plan, names, rows)
+            x = gt.transformer[0].post(ops.row_gather(x1_tab, plan, names, rows), ops.row_gather(qkv_tab, plan, names, rows),
+                                       T, n_seq, outer_residual=x_in if n_blocks == 1 else None, outer_feats=self.n_feats)
+            first = 1
+        else:
+            x_in = ops.tuple_gather(atom_feats, plan, level, n_seq, self.n_feats, self.trafo_out_feats,
+                                    None if pe is None else pe.reshape(-1).contiguous())
+            x = x_in
+            first = 0
+        for i in range(first, n_blocks):
             last = i == n_blocks - 1
-            x = blk(x, T, n_seq, outer_residual=x_in if last else None, outer_feats=self.n_feats)
+            x = gt.transformer[i](x, T, n_seq, outer_residual=x_in if last else None, outer_feats=self.n_feats)
         x = ops.layer_norm(x, self.norm.weight, self.norm.bias)
         return self.symmetriser(x, T)
+
+
+def _dedup_tables(self, plan, level, n_atoms, n_tokens):
+    """Plan array names (idx, ptr, tok) of the distinct-content table of `level`, or None when de-duplication does not pay
+    or the positional encoding is not the pattern the plan was built for."""
+    if not DEDUP_TOKENS or n_tokens == 0:
+        return None
+    pe = self.grappa_transformer.positional_encoding
+    if pe is None:
+        if self.trafo_out_feats != self.n_feats or n_tokens < DEDUP_RATIO * n_atoms:
+            return None
+        return ("idx_" + level, "inc_ptr_" + level, "inc_tok_" + level)
+    pattern = PE_PATTERN.get(level)
+    if pattern is None or ("tab_idx_" + level) not in plan.offsets or n_tokens < DEDUP_RATIO * 2 * n_atoms:
+        return None
+    if getattr(self, "_pe_host", None) is None:
+        self._pe_host = tuple(float(v) for v in pe.detach().flatten().tolist())
+    if self._pe_host != tuple(float(v) for v in pattern):
+        return None
+    return ("tab_idx_" + level, "tab_ptr_" + level, "tab_tok_" + level)
+
+
+SymmetrisedTransformer._dedup_tables = _dedup_tables
 
 
 class ToPositive(nn.Module):

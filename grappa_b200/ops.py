@@ -361,6 +361,58 @@ def tuple_gather(a, plan, level, n_seq, F, W, pe=None):
     return TupleGatherFn.apply(a, plan, level, n_seq, F, W, pe)
 
 
+class PeTableFn(torch.autograd.Function):
+    """U[2a + pe] = [P[a, :F], pe] for pe in {0, 1}: the distinct transformer inputs of a level with a PE column."""
+
+    @staticmethod
+    def forward(ctx, a, F, W):
+        a, lda = _rows2d(a, "atom_feats")
+        N = a.shape[0]
+        u = torch.empty((2 * N, W), device=a.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_pe_table_fwd(N, F, W, _p(a), lda, _p(u), _stream()))
+        ctx.cfg = (N, F, W, lda)
+        return u
+
+    @staticmethod
+    def backward(ctx, du):
+        N, F, W, lda = ctx.cfg
+        du = du.contiguous()
+        ldda = max(lda, W)
+        da = torch.empty((N, ldda), device=du.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_pe_table_bwd(N, F, W, _p(du), _p(da), ldda, _stream()))
+        return da, None, None
+
+
+def pe_table(a, F, W):
+    return PeTableFn.apply(a, F, W)
+
+
+class RowGatherFn(torch.autograd.Function):
+    """X[r] = table[idx[r]] with a pull-style, fixed-order backward over the CSR (ptr, tok) of idx."""
+
+    @staticmethod
+    def forward(ctx, table, plan, names, rows):
+        table, ldt = _rows2d(table, "table")
+        D = table.shape[1]
+        x = torch.empty((rows, D), device=table.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_row_gather_fwd(rows, D, _p(table), ldt, plan.ptr(names[0]), _p(x), D, _stream()))
+        ctx.cfg = (plan, names, table.shape[0], D)
+        return x
+
+    @staticmethod
+    def backward(ctx, dx):
+        plan, names, R, D = ctx.cfg
+        dx = dx.contiguous()
+        dt = torch.empty((R, D), device=dx.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_row_gather_bwd(R, D, _p(dx), D, plan.ptr(names[1]), plan.ptr(names[2]), _p(dt), D, _stream()))
+        return dt, None, None, None
+
+
+def row_gather(table, plan, names, rows):
+    """names = (idx, ptr, tok) array names of the batch plan."""
+    return RowGatherFn.apply(table, plan, names, rows)
+
+
 class TupleAttnFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, T, n_seq, n_heads):

@@ -6,6 +6,8 @@ buffer and moved to the device with a single copy:
   - idxs narrowed to int32 per level                         (gather / VJP kernels)
   - CSR of the directed bond edges by destination and by source   (graph attention fwd / bwd)
   - atom -> token-row incidence CSR per level                (pull-style backward of the tuple gather)
+  - (atom, pe) table row per token + its CSR for the levels with a positional-encoding column
+                                                             (token de-duplication of the first LayerNorm + QKV)
   - the energy kernel's atom-block / tuple-record / staging-slot tables  (grappa_energy_plan_build)
   - per-molecule offsets of atoms / proper / improper rows   (segmenting, fused loss)
 
@@ -23,6 +25,9 @@ from . import _lib
 from .graph import LEVELS, N_SEQ, get_bond_edges
 
 ENERGY_BLOCK_ATOMS = 64
+# positional-encoding column of the default architecture per level (perm_equiv_transformer.py:189-199); bonds have none.
+# The (atom, pe) token tables below are built for these patterns; a model with another encoding does not use them.
+PE_PATTERN = {"n3": (0, 1, 0), "n4": (0, 1, 1, 0), "n4_improper": (0, 1, 1, 0)}
 
 
 def _np_ptr(a: np.ndarray):
@@ -118,6 +123,15 @@ def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS) -> BatchPlan:
                                       _np_ptr(inc_tok)))
         arrays["inc_ptr_" + lvl] = inc_ptr
         arrays["inc_tok_" + lvl] = inc_tok
+        if lvl in PE_PATTERN:
+            # table row of a token = 2 * atom + pe(position): composes under batching with the offset 2 * atom_offset
+            keys = np.ascontiguousarray((2 * ix + np.asarray(PE_PATTERN[lvl], np.int64)[None, :]).reshape(-1))
+            tab_ptr = np.zeros(2 * n_atoms + 1, np.int32)
+            tab_tok = np.zeros(ix.size, np.int32)
+            _lib.check(L.grappa_csr_build(ix.size, 2 * n_atoms, _np_ptr(keys), _np_ptr(tab_ptr), _np_ptr(tab_tok)))
+            arrays["tab_idx_" + lvl] = keys.astype(np.int32)
+            arrays["tab_ptr_" + lvl] = tab_ptr
+            arrays["tab_tok_" + lvl] = tab_tok
     p.levels_present = tuple(present)
 
     # bond edges -> CSR by destination / by source

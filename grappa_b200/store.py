@@ -198,6 +198,9 @@ class MoleculeStore:
             lengths["inc_ptr_" + lvl] = nA + 1
             lengths["inc_tok_" + lvl] = N_SEQ[lvl] * plan.T[lvl]
             lengths["mol_off_" + lvl] = B + 1
+            lengths["tab_idx_" + lvl] = N_SEQ[lvl] * plan.T[lvl]
+            lengths["tab_ptr_" + lvl] = 2 * nA + 1
+            lengths["tab_tok_" + lvl] = N_SEQ[lvl] * plan.T[lvl]
         lengths.update(in_ptr=nA + 1, out_ptr=nA + 1, in_nbr=nE, out_nbr=nE, e_blk=12 * int(Bc[-1]),
                        e_rec_atoms=4 * int(Rc[-1]), e_rec_meta=2 * int(Rc[-1]), e_rec_slot=4 * int(Rc[-1]),
                        e_pull_ptr=nA + 1, e_pull_slot=int(Pc[-1]), tuple_mol=T_all, mol_atom_off=B + 1)
@@ -237,6 +240,15 @@ class MoleculeStore:
                 lvl = name[8:]
                 seg(name, Ac[:-1], ln, 0, N_SEQ[lvl] * Tc[lvl][:-1])
             elif name.startswith("inc_tok_"):
+                lvl = name[8:]
+                seg(name, N_SEQ[lvl] * Tc[lvl][:-1], ln, 0, N_SEQ[lvl] * Tc[lvl][:-1])
+            elif name.startswith("tab_idx_"):
+                lvl = name[8:]
+                seg(name, N_SEQ[lvl] * Tc[lvl][:-1], ln, 0, 2 * Ac[:-1])
+            elif name.startswith("tab_ptr_"):
+                lvl = name[8:]
+                seg(name, 2 * Ac[:-1], ln, 0, N_SEQ[lvl] * Tc[lvl][:-1])
+            elif name.startswith("tab_tok_"):
                 lvl = name[8:]
                 seg(name, N_SEQ[lvl] * Tc[lvl][:-1], ln, 0, N_SEQ[lvl] * Tc[lvl][:-1])
             elif name in ("in_ptr", "out_ptr"):

@@ -120,6 +120,19 @@ int grappa_tuple_gather_fwd(int64_t T, int n_seq, int F, int W, const float* A, 
 int grappa_tuple_gather_bwd(int64_t N, int F, int W, const float* dX, const int32_t* inc_ptr, const int32_t* inc_tok,
                             float* dA, int64_t ldda, void* stream);
 
+/* Token de-duplication for the first LayerNorm + QKV projection of a writer's transformer
+ * (perm_equiv_transformer.py:152-165 with network_utils.py:119-123): a token's content depends only on (atom,
+ * positional-encoding value), so these two layers run once per table row (2 N rows, or N without a PE column) and
+ * are gathered per token.  No counterpart in the reference, which projects every token.
+ *   pe_table:   U[2a+pe, c] = c < F ? P[a, c] : pe   (U: (2N, W) dense);  bwd: dP[a, c<F] = dU[2a, c] + dU[2a+1, c]
+ *   row_gather: X[r, :] = table[idx[r], :];  bwd (pull, fixed order): dTable[j, :] = sum_{q in ptr[j]..ptr[j+1]} dX[tok[q], :] */
+int grappa_pe_table_fwd(int64_t N, int F, int W, const float* P, int64_t ldp, float* U, void* stream);
+int grappa_pe_table_bwd(int64_t N, int F, int W, const float* dU, float* dP, int64_t lddp, void* stream);
+int grappa_row_gather_fwd(int64_t rows, int D, const float* table, int64_t ldt, const int32_t* idx, float* X,
+                          int64_t ldx, void* stream);
+int grappa_row_gather_bwd(int64_t table_rows, int D, const float* dX, int64_t ldx, const int32_t* ptr,
+                          const int32_t* tok, float* dTable, int64_t ldt, void* stream);
+
 /* Self-attention over the n_seq <= 4 tokens of every tuple (nn.MultiheadAttention core, network_utils.py:123).
  * qkv: (T*n_seq, 3*E) = [q | k | v], E = n_heads*head_dim, head_dim 64.  out: (T*n_seq, E). */
 int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, float* out, void* stream);

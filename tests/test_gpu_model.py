@@ -278,3 +278,34 @@ def test_bucketed_gradient_exchange_choreography(use_graph):
     assert outs["plain"][0] == outs["overlap_noop"][0] == outs["overlap_double"][0]
     assert torch.equal(outs["plain"][1], outs["overlap_noop"][1])
     assert torch.equal(outs["plain"][1] * 2.0, outs["overlap_double"][1])
+
+
+def test_token_deduplication_is_exact_in_forward_and_consistent_in_backward(monkeypatch):
+    """Running the first LayerNorm + QKV projection once per distinct (atom, pe) row and gathering per token gives
+    bit-identical parameters (row-wise arithmetic) and the same parameter gradients up to summation order."""
+    import grappa_b200.model as M
+    g_host = batch([S.trimer_molecule(seed=s, n_confs=3) for s in range(3)])
+    results = {}
+    for dedup in (False, True):
+        monkeypatch.setattr(M, "DEDUP_TOKENS", dedup)
+        model, _ = build_model(train=True)
+        for m in model.modules():
+            if isinstance(m, torch.nn.Dropout):
+                m.p = 0.0
+        calls = []
+        orig = ops.row_gather
+        monkeypatch.setattr(ops, "row_gather", lambda *a, **k: (calls.append(1), orig(*a, **k))[1])
+        g = batch([S.trimer_molecule(seed=s, n_confs=3) for s in range(3)]).to(DEV)
+        loss, g = train_loss(model, g)
+        loss.backward()
+        monkeypatch.setattr(ops, "row_gather", orig)
+        assert (len(calls) > 0) == dedup                      # bonds, angles and propers qualify at this size
+        results[dedup] = (graph_params(g), float(loss), {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None})
+    for lvl in LEVELS:
+        for key, v in results[False][0][lvl].items():
+            assert torch.equal(v, results[True][0][lvl][key]), f"{lvl} {key}"
+    assert results[False][1] == results[True][1]
+    for n, gr in results[False][2].items():
+        scale = float(gr.abs().max()) + 1e-12
+        err = float((gr - results[True][2][n]).abs().max()) / scale
+        assert err < 2e-4, f"{n}: {err:.2e}"

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 
 from grappa_b200 import ops, synthetic as S
 from grappa_b200.graph import batch
-from grappa_b200.plan import build_plan
+from grappa_b200.plan import build_plan, get_plan
 
 DEV = "cuda"
 
@@ -332,3 +332,44 @@ def test_empty_inputs_are_handled():
     assert ops.linear(x, w).shape == (0, 256)
     assert ops.layer_norm(x, torch.ones(512, device=DEV), torch.zeros(512, device=DEV)).shape == (0, 512)
     assert ops.tuple_attention(torch.zeros((0, 1536), device=DEV), 0, 3, 8).shape == (0, 512)
+
+
+def test_pe_table_and_row_gather_ops():
+    """Token de-duplication helpers: the (atom, pe) table and the row gather with its pull-style backward."""
+    from grappa_b200.plan import PE_PATTERN
+    g = batch([S.trimer_molecule(s, 2) for s in (0, 1)]).to(DEV)
+    plan = get_plan(g)
+    N = g.num_nodes("n1")
+    torch.manual_seed(0)
+    for level, n_seq in (("n3", 3), ("n4", 4), ("n4_improper", 4)):
+        T = plan.T[level]
+        P = torch.randn(N, 512, device=DEV, requires_grad=True)
+        U = ops.pe_table(P, 511, 512)
+        ref_U = torch.stack([torch.cat([P[:, :511], torch.full((N, 1), float(pe), device=DEV)], 1) for pe in (0, 1)], 1).reshape(2 * N, 512)
+        assert torch.equal(U, ref_U)
+        names = ("tab_idx_" + level, "tab_ptr_" + level, "tab_tok_" + level)
+        X = ops.row_gather(U, plan, names, T * n_seq)
+        idx = g.nodes[level].data["idxs"].long()
+        pe = torch.tensor(PE_PATTERN[level], device=DEV)
+        rows = (2 * idx + pe[None, :]).reshape(-1)
+        assert torch.equal(plan.view(names[0]).long(), rows)
+        assert torch.equal(X, ref_U[rows])
+        # the same tokens as the direct gather of the writers
+        direct = ops.tuple_gather(P, plan, level, n_seq, 511, 512, pe.float())
+        assert torch.equal(X, direct)
+        w = torch.randn_like(X)
+        (X * w).sum().backward()
+        Pr = P.detach().clone().requires_grad_(True)
+        Ur = torch.stack([torch.cat([Pr[:, :511], torch.full((N, 1), float(q), device=DEV)], 1) for q in (0, 1)], 1).reshape(2 * N, 512)
+        (Ur[rows] * w).sum().backward()
+        torch.testing.assert_close(P.grad, Pr.grad, rtol=1e-5, atol=1e-5)
+    # wide rows (the QKV table) through the bond-level incidence lists, i.e. no PE column
+    tab = torch.randn(N, 1536, device=DEV, requires_grad=True)
+    names = ("idx_n2", "inc_ptr_n2", "inc_tok_n2")
+    X = ops.row_gather(tab, plan, names, plan.T["n2"] * 2)
+    rows = g.nodes["n2"].data["idxs"].long().reshape(-1)
+    assert torch.equal(X, tab[rows])
+    w = torch.randn_like(X)
+    (X * w).sum().backward()
+    ref = torch.zeros_like(tab).index_add_(0, rows, w)
+    torch.testing.assert_close(tab.grad, ref, rtol=1e-5, atol=1e-5)
