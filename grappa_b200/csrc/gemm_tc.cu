@@ -228,10 +228,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int nk = min(kb_per_split, nk_total - kb_begin);
     const int n_chunks = (nk + KB_PER_CHUNK - 1) / KB_PER_CHUNK;
 
+    // one k-block of raw operand tiles into stage kb % STAGES (issued by thread 0 only)
+    auto issue_loads = [&](int kb) {
+        const int s = kb % STAGES;
+        uint8_t* st = smem + s * STAGE_BYTES;
+        mbar_expect_tx(&full[s], 2 * TILE_BYTES);
+        const int k0 = (kb_begin + kb) * BK;
+        if (!A_MN) {
+            tma_load_2d(st, &mapA, &full[s], k0, m0);
+        } else {
+#pragma unroll
+            for (int j = 0; j < BM / 32; ++j) tma_load_2d(st + j * (BK * 128), &mapA, &full[s], m0 + 32 * j, k0);
+        }
+        if (!B_MN) {
+            tma_load_2d(st + 2 * TILE_BYTES, &mapB, &full[s], k0, n0);
+        } else {
+#pragma unroll
+            for (int j = 0; j < BN / 32; ++j) tma_load_2d(st + 2 * TILE_BYTES + j * (BK * 128), &mapB, &full[s], n0 + 32 * j, k0);
+        }
+    };
+
     if (threadIdx.x == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapB)) : "memory");
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&split[s], 128); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&chunk_full[b], 1); mbar_init(&chunk_empty[b], 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // the ring is empty: fill it right away, in the shadow of the TMEM allocation and the CTA-wide barrier below
+        for (int kb = 0; kb < min(nk, STAGES); ++kb) issue_loads(kb);
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
@@ -246,24 +270,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
-            for (int kb = 0; kb < nk; ++kb) {
-                const int s = kb % STAGES;
-                if (kb >= STAGES) mbar_wait(&empty[s], ((kb / STAGES) - 1) & 1);
-                uint8_t* st = smem + s * STAGE_BYTES;
-                mbar_expect_tx(&full[s], 2 * TILE_BYTES);
-                const int k0 = (kb_begin + kb) * BK;
-                if (!A_MN) {
-                    tma_load_2d(st, &mapA, &full[s], k0, m0);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < BM / 32; ++j) tma_load_2d(st + j * (BK * 128), &mapA, &full[s], m0 + 32 * j, k0);
-                }
-                if (!B_MN) {
-                    tma_load_2d(st + 2 * TILE_BYTES, &mapB, &full[s], k0, n0);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < BN / 32; ++j) tma_load_2d(st + 2 * TILE_BYTES + j * (BK * 128), &mapB, &full[s], n0 + 32 * j, k0);
-                }
+            for (int kb = min(nk, STAGES); kb < nk; ++kb) {           // the first STAGES loads went out before the CTA barrier
+                mbar_wait(&empty[kb % STAGES], ((kb / STAGES) - 1) & 1);
+                issue_loads(kb);
             }
         }
     } else if (warp == 1) {
