@@ -365,6 +365,56 @@ def collate_bench(ts, dev, K):
                     "store; the host uploads only the segment tables"}
 
 
+def hbm_kernels(g, pk):
+    """The gather / scatter kernels of the path timed alone at cfg-3 size (15 k atoms) against the HBM roofline:
+    algorithmic bytes (K1 = (2N + E) * 2048 B; gathers = one read of the source rows + one write of the
+    tokens) / device time from CUDA events over back-to-back launches.  Inputs exceed L2 or are rotated, no flush."""
+    from grappa_b200 import ops
+    from grappa_b200.plan import get_plan
+    dev = g.nodes["n1"].data["partial_charge"].device
+    plan = get_plan(g)
+    N, E = plan.n_atoms, plan.n_edges
+    res = {}
+
+    def timed(fn, n=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+
+    with torch.no_grad():
+        fts = [torch.randn(N, 512, device=dev) for _ in range(8)]          # 8 x 31 MB rotated: beyond L2 reuse
+        i = [0]
+        def k1():
+            i[0] = (i[0] + 1) % len(fts)
+            ops.gnn_attention(fts[i[0]], plan, 16)
+        ms = timed(k1)
+        byts = (2 * N + E) * 2048
+        res["gnn_attn_fwd"] = {"ms": ms, "algorithmic_bytes": byts, "GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / pk["hbm_gbs"]}
+        T4 = plan.T["n4"]
+        names = ("tab_idx_n4", "tab_ptr_n4", "tab_tok_n4")
+        tab = torch.randn(2 * N, 1536, device=dev)                          # the QKV table of the proper torsions
+        ms = timed(lambda: ops.row_gather(tab, plan, names, 4 * T4))
+        byts = (2 * N + 4 * T4) * 1536 * 4 + 4 * T4 * 4
+        res["row_gather_fwd_qkv_n4"] = {"ms": ms, "algorithmic_bytes": byts, "GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / pk["hbm_gbs"]}
+        qkv = torch.randn(4 * T4, 1536, device=dev)
+        ms = timed(lambda: ops.tuple_attention(qkv, T4, 4, 8))
+        byts = 4 * T4 * (1536 + 512) * 4
+        res["tuple_attn_fwd_n4"] = {"ms": ms, "algorithmic_bytes": byts, "GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / pk["hbm_gbs"]}
+        x = torch.randn(4 * T4, 512, device=dev)
+        gam, bet = torch.ones(512, device=dev), torch.zeros(512, device=dev)
+        ms = timed(lambda: ops.layer_norm(x, gam, bet))
+        byts = 4 * T4 * 512 * 4 * 2
+        res["layernorm_fwd_tokens_n4"] = {"ms": ms, "algorithmic_bytes": byts, "GBps": byts / ms / 1e6, "hbm_frac": byts / ms / 1e6 / pk["hbm_gbs"]}
+    return res
+
+
 def extras(dev, pk):
     """BASELINE.json configs[2] (inference atoms/s, 15k-atom system) and configs[3] (energy sweep, 1000 x 500)."""
     from grappa_b200 import synthetic as S
@@ -388,6 +438,7 @@ def extras(dev, pk):
     ms = a.elapsed_time(b) / n
     out["inference_cfg3"] = {"atoms": g.num_nodes("n1"), "ms": ms, "atoms_per_s": g.num_nodes("n1") / (ms * 1e-3),
                              "algorithmic_tflop": 1.7, "tflops": 1.7 / (ms * 1e-3)}
+    out["hbm_kernels_cfg3"] = hbm_kernels(g, pk)
     del g
     g4 = S.cfg4_batch(1000, 500).to(dev)
     k_src = S.trimer_molecule(0, 1).to(dev)
