@@ -309,3 +309,46 @@ def test_token_deduplication_is_exact_in_forward_and_consistent_in_backward(monk
         scale = float(gr.abs().max()) + 1e-12
         err = float((gr - results[True][2][n]).abs().max()) / scale
         assert err < 2e-4, f"{n}: {err:.2e}"
+
+
+def test_drop_in_on_a_dgl_style_graph_object(golden_dir):
+    """The modules only touch the accessor surface SURVEY.md §8b lists (ntypes, num_nodes, nodes[t].data, edges(etype),
+    batch_num_nodes, to), so they must work on a DGL heterograph as well as on this package's container.  Real DGL is not
+    installable here; the test infrastructure's pure-PyTorch stand-in with DGL's API (oracle/dgl_standin, the same object
+    the unmodified reference ran on when the goldens were made) takes its place, for one molecule and for `dgl.batch`."""
+    import sys
+    standin = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle", "dgl_standin")
+    if standin not in sys.path:
+        sys.path.insert(0, standin)
+    import dgl
+    assert "standin" in dgl.__version__
+    from make_golden import to_reference_graph
+    gold = np.load(os.path.join(golden_dir, "cfg1_forward.npz"))
+    model, _ = build_model()
+    en = Energy(terms=["bond", "angle", "proper", "improper"])
+    g = to_reference_graph(S.cfg1_graph(n_confs=5, seed=0)).to(DEV)
+    assert type(g).__module__.startswith("dgl")
+    with torch.no_grad():
+        out = en(model(g))
+    assert out is g                                           # same object, mutated (models/grappa.py:189)
+    want = {l: {k: gold[f"{l}_{k}"] for k in (("k", "eq") if l in ("n2", "n3") else ("k",))} for l in LEVELS}
+    assert_params_close(graph_params(g), want, "golden, dgl-style graph")
+    np.testing.assert_allclose(g.nodes["g"].data["energy"].cpu().numpy(), gold["g_energy"], rtol=1e-4, atol=5e-2)
+    np.testing.assert_allclose(g.nodes["n1"].data["gradient"].cpu().numpy(), gold["gradient"], rtol=1e-4, atol=2e-2)
+    # a batch made by the DGL-style `batch` (idxs offset by the caller as utils/dgl_utils.py:57-59 does)
+    mols = [S.trimer_molecule(seed=s, n_confs=3) for s in (0, 1)]
+    ours = batch(mols).to(DEV)
+    refs = [to_reference_graph(m) for m in mols]
+    off = 0
+    for r in refs:
+        for lvl in LEVELS:
+            r.nodes[lvl].data["idxs"] = r.nodes[lvl].data["idxs"] + off
+        off += r.num_nodes("n1")
+    gb = dgl.batch(refs).to(DEV)
+    with torch.no_grad():
+        a, b = en(model(ours)), en(model(gb))
+    for lvl in LEVELS:
+        for key, v in graph_params(a)[lvl].items():
+            assert torch.equal(v, graph_params(b)[lvl][key]), f"{lvl} {key}"
+    assert torch.equal(a.nodes["g"].data["energy"], b.nodes["g"].data["energy"])
+    assert torch.equal(a.nodes["n1"].data["gradient"], b.nodes["n1"].data["gradient"])
