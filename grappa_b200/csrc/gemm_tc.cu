@@ -607,10 +607,11 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
     const int64_t tiles = ceil_div(p.N, BN) * ceil_div(p.M, BM);
     const int nk = (int)ceil_div(p.K, BK);
     // split K when the tile grid leaves most of the 148 SMs idle and the k loop is long enough to amortise the
-    // extra pass; slices are multiples of the promotion chunk
+    // extra pass; slices are multiples of the promotion chunk.  tiles * splits stays <= 148 (one CTA per SM): one CTA
+    // more than that costs a whole second wave (measured: 40 tiles x 4 slices = 160 CTAs 42 us, x 3 slices 29 us).
     int splits = 1;
     if (workspace != nullptr && tiles <= 74 && nk >= 32) {
-        const int want = (int)std::min<int64_t>(ceil_div(148, tiles), nk / 16);
+        const int want = (int)std::min<int64_t>(148 / tiles, nk / 16);
         if (want > 1 && (int64_t)want * p.M * p.N <= workspace_floats) splits = want;
     }
     int kps = nk;
