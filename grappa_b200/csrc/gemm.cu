@@ -173,6 +173,7 @@ __global__ void __launch_bounds__(256) sgemm_kernel(GemmParams p, int64_t k_per_
                     if (has_drop) z = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? z * p.drop_scale : 0.f;
                     if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n + j);
                     if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n + j);
+                    if (p.elu_out) z *= elu_grad_from_out(__ldg(p.elu_out + m * p.ld_eo + n + j));
                     v[j] = z;
                 }
             }
@@ -217,11 +218,12 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 
 using namespace grappa;
 
-extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
+static int gemm_impl(int layout, int64_t M, int64_t N, int64_t K,
                            const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
                            const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
                            float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
-                           float* workspace, int64_t workspace_floats, void* stream) {
+                           float* workspace, int64_t workspace_floats, void* stream,
+                           const float* elu_out, int64_t ld_eo) {
     GRAPPA_CHECK_ARG(layout >= 0 && layout <= 2, "layout must be 0 (NT), 1 (NN) or 2 (TN)");
     GRAPPA_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "negative size");
     GRAPPA_CHECK_ARG(act == 0 || act == 1, "act must be 0 (none) or 1 (ELU)");
@@ -233,6 +235,7 @@ extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
     p.A = A; p.B = B; p.C = C; p.bias = bias; p.res1 = res1; p.res2 = res2;
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldr1 = ldr1; p.ldr2 = ldr2;
     p.act = act; p.drop_p = drop_p; p.drop_scale = 1.0f / (1.0f - drop_p); p.seed = seed; p.seed_dev = seed_dev;
+    p.elu_out = elu_out; p.ld_eo = ld_eo;
     p.a_vec = aligned16(A) && (lda % 4 == 0);
     p.b_vec = aligned16(B) && (ldb % 4 == 0);
     p.c_vec = aligned16(C) && (ldc % 4 == 0);
@@ -247,4 +250,22 @@ extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
     const int64_t big_ctas = ceil_div(M, 128) * ceil_div(N, 128);
     if (big_ctas >= 120) return launch_layout<128, 128, 16, 8, 8>(layout, p, st, workspace, workspace_floats);
     return launch_layout<64, 64, 16, 4, 4>(layout, p, st, workspace, workspace_floats);
+}
+
+extern "C" int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
+                           const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                           const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                           float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                           float* workspace, int64_t workspace_floats, void* stream) {
+    return gemm_impl(layout, M, N, K, A, lda, B, ldb, C, ldc, bias, act, res1, ldr1, res2, ldr2, drop_p, seed, seed_dev, math_mode,
+                     workspace, workspace_floats, stream, nullptr, 0);
+}
+
+extern "C" int grappa_gemm_actgrad(int layout, int64_t M, int64_t N, int64_t K,
+                                   const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                                   const float* elu_out, int64_t ld_eo, int math_mode,
+                                   float* workspace, int64_t workspace_floats, void* stream) {
+    GRAPPA_CHECK_ARG(elu_out != nullptr && ld_eo >= N, "elu_out (M, N) with ld_eo >= N is required");
+    return gemm_impl(layout, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, nullptr, 0, nullptr, 0, 0.f, 0, nullptr, math_mode,
+                     workspace, workspace_floats, stream, elu_out, ld_eo);
 }

@@ -10,7 +10,12 @@ struct GemmParams {
     int64_t M, N, K, lda, ldb, ldc, ldr1, ldr2;
     int act; float drop_p; float drop_scale; uint64_t seed; const uint64_t* seed_dev;
     int a_vec, b_vec, c_vec;   // 16-byte vector access allowed for A / B / (C, res)
+    // optional last epilogue step (backward GEMMs): C *= ELU'(pre-activation) read off the saved ELU OUTPUT s:
+    // ELU'(x) = 1 for x > 0, exp(x) = s + 1 otherwise
+    const float* elu_out = nullptr; int64_t ld_eo = 0;
 };
+
+__device__ __forceinline__ float elu_grad_from_out(float s) { return s > 0.f ? 1.f : s + 1.f; }
 
 int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
                      bool* handled);   // gemm_tc.cu

@@ -186,6 +186,33 @@ __device__ __forceinline__ void writeout_interior(const GemmParams& p, uint32_t 
     }
 }
 
+// interior tile of a backward GEMM: C = acc * ELU'(.) from the saved ELU output (no bias / activation / residual)
+__device__ __forceinline__ void writeout_interior_actgrad(const GemmParams& p, uint32_t tile, int warp, int lane, int m0, int n0) {
+    constexpr int RPI = 4, PASS = (THREADS / 32) * RPI;
+    const int64_t n = (int64_t)n0 + lane * 4;
+    const int64_t mrow = (int64_t)m0 + warp * RPI;
+    float* cp = p.C + mrow * p.ldc + n;
+    const float* ep = p.elu_out + mrow * p.ld_eo + n;
+    uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
+#pragma unroll 1
+    for (int r0 = warp * RPI; r0 < BM; r0 += PASS) {
+        float4 a[RPI], e[RPI];
+#pragma unroll
+        for (int i = 0; i < RPI; ++i) {
+            a[i] = lds128(ts + i * (EPI_LD * 4));
+            e[i] = __ldg(reinterpret_cast<const float4*>(ep + i * p.ld_eo));
+        }
+#pragma unroll
+        for (int i = 0; i < RPI; ++i)
+            *reinterpret_cast<float4*>(cp + i * p.ldc) =
+                make_float4(a[i].x * elu_grad_from_out(e[i].x), a[i].y * elu_grad_from_out(e[i].y),
+                            a[i].z * elu_grad_from_out(e[i].z), a[i].w * elu_grad_from_out(e[i].w));
+        ts += PASS * (EPI_LD * 4);
+        cp += PASS * p.ldc;
+        ep += PASS * p.ld_eo;
+    }
+}
+
 template <int NRES>
 __device__ __forceinline__ void writeout_interior_dispatch(const GemmParams& p, uint32_t tile, int warp, int lane, int m0, int n0,
                                                            uint64_t seed, bool act, bool drop) {
@@ -452,7 +479,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const bool al1 = !p.res1 || ((p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0));
             const bool al2 = !p.res2 || ((p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0));
             const bool alb = !p.bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-            if (p.c_vec && al1 && al2 && alb && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N && !(p.res2 && !p.res1)) {
+            const bool interior = p.c_vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N;
+            if (interior && p.elu_out && !p.bias && !p.res1 && !p.res2 && p.act == 0 && !has_drop && (p.ld_eo % 4 == 0) &&
+                ((reinterpret_cast<uintptr_t>(p.elu_out) & 15) == 0)) {
+                writeout_interior_actgrad(p, tile, warp, lane, m0, n0);
+            } else if (interior && !p.elu_out && al1 && al2 && alb && !(p.res2 && !p.res1)) {
                 const bool act = p.act == 1;
                 if (p.res2) writeout_interior_dispatch<2>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
                 else if (p.res1) writeout_interior_dispatch<1>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
@@ -514,6 +545,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
                             v[j] = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? v[j] * p.drop_scale : 0.f;
                     }
                     v[0] = (v[0] + q1[i].x) + q2[i].x; v[1] = (v[1] + q1[i].y) + q2[i].y; v[2] = (v[2] + q1[i].z) + q2[i].z; v[3] = (v[3] + q1[i].w) + q2[i].w;
+                    if (p.elu_out) {
+                        const float* ep = p.elu_out + m * p.ld_eo + n;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (j < nvalid) v[j] *= elu_grad_from_out(__ldg(ep + j));
+                    }
                     float* cp = p.C + m * p.ldc + n;
                     if (p.c_vec && nvalid == 4) {
                         *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
@@ -559,6 +596,7 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmParams p, int sp
         if (has_drop) z = hash_uniform(seed, (uint64_t)i) >= p.drop_p ? z * p.drop_scale : 0.f;
         if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n);
         if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n);
+        if (p.elu_out) z *= elu_grad_from_out(__ldg(p.elu_out + m * p.ld_eo + n));
         p.C[m * p.ldc + n] = z;
     }
 }

@@ -112,8 +112,7 @@ class ResidualAttentionBlock(nn.Module):
         h = ops.linear(att, self.head_reducer.weight, self.head_reducer.bias, res1=h, drop_p=p1)
         h = ops.layer_norm(h, self.interaction_norm.weight, self.interaction_norm.bias)
         lin1, lin2 = self.self_interaction[0], self.self_interaction[2]
-        u = ops.linear(h, lin1.weight, lin1.bias, act=ops.ACT_ELU)
-        return ops.linear(u, lin2.weight, lin2.bias, act=ops.ACT_ELU, res1=h, drop_p=p2)
+        return ops.elu_mlp(h, lin1.weight, lin1.bias, lin2.weight, lin2.bias, act2=ops.ACT_ELU, res1=h, drop_p=p2)
 
 
 class ChargeEncoding(nn.Module):
@@ -228,9 +227,8 @@ class FeedForwardLayer(nn.Module):
         """network_utils.py:44-54.  `extra_residual` is added in the same GEMM epilogue (callers' outer skips)."""
         p = self.dropout.p if self.training else 0.0
         n = ops.layer_norm(x, self.norm1.weight, self.norm1.bias)
-        z = ops.linear(n, self.linear1.weight, self.linear1.bias, act=ops.ACT_ELU)
-        return ops.linear(z, self.linear2.weight, self.linear2.bias, res1=n if self.skip else None, res2=extra_residual,
-                          drop_p=p)
+        return ops.elu_mlp(n, self.linear1.weight, self.linear1.bias, self.linear2.weight, self.linear2.bias,
+                           res1=n if self.skip else None, res2=extra_residual, drop_p=p)
 
 
 class _MHAParams(nn.Module):

@@ -18,6 +18,7 @@ ACT_NONE, ACT_ELU = 0, 1
 # (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
 # Valid because every parameter of the model is used exactly once per forward.
 GRAD_SINK = None
+FUSE_ELU_GRAD = _os.environ.get("GRAPPA_FUSE_ELU_GRAD", "1") != "0"      # Linear-ELU-Linear blocks: ELU' of the hidden tensor in the dX GEMM epilogue (see LinearFn)
 # With a gradient sink nothing downstream in autograd consumes parameter gradients, so the weight-gradient GEMM, the
 # bias column sum and the LayerNorm affine reductions are issued on a side stream and overlap with the activation-
 # gradient chain (most of these kernels have far fewer tiles than SMs).  The step driver joins the side stream after
@@ -34,21 +35,44 @@ def norm_device(device) -> torch.device:
     return device
 
 
+SIDE_STREAM_PER_STREAM = _os.environ.get("GRAPPA_SIDE_PER_STREAM", "1") != "0"
+SIDE_POOL = int(_os.environ.get("GRAPPA_SIDE_POOL", "1"))      # side streams per compute stream, used round-robin
+_SIDE_RR = {}
+
+
 def _side_stream(device):
+    """The side stream paired with the CURRENT stream: the four writers run on four streams, and one shared side stream
+    would serialise their parameter-gradient work (and delay the GNN's behind it)."""
     device = norm_device(device)
-    st = _SIDE_STREAMS.get(device)
+    cs = torch.cuda.current_stream(device).cuda_stream if SIDE_STREAM_PER_STREAM else 0
+    slot = 0
+    if SIDE_POOL > 1:
+        slot = _SIDE_RR.get((device, cs), 0)
+        _SIDE_RR[(device, cs)] = (slot + 1) % SIDE_POOL
+    key = (device, (cs, slot))
+    st = _SIDE_STREAMS.get(key)
     if st is None:
         st = torch.cuda.Stream(device=device)
-        _SIDE_STREAMS[device] = st
+        _SIDE_STREAMS[key] = st
     return st
+
+
+_ACTIVE_SIDE = {}          # side streams that received work since the last join (stale ones must not be waited on
+                           # under graph capture: "dependency on uncaptured work")
+
+
+def side_streams(device):
+    """Side streams of `device` with gradient work pending since the last join."""
+    device = norm_device(device)
+    return [st for (d, _), st in _ACTIVE_SIDE.items() if d == device]
 
 
 def join_side_work(device):
     """Make the current stream wait for all side-stream gradient work; called once after backward."""
     device = norm_device(device)
-    st = _SIDE_STREAMS.get(device)
-    if st is not None:
-        torch.cuda.current_stream(device).wait_stream(st)
+    cur = torch.cuda.current_stream(device)
+    for key in [k for k in _ACTIVE_SIDE if k[0] == device]:
+        cur.wait_stream(_ACTIVE_SIDE.pop(key))
     _DEFERRED.clear()
 
 
@@ -60,6 +84,7 @@ class _on_side_stream:
     def __enter__(self):
         cur = torch.cuda.current_stream(self.device)
         side = _side_stream(self.device)
+        _ACTIVE_SIDE[(norm_device(self.device), side.cuda_stream)] = side
         ev = torch.cuda.Event()
         ev.record(cur)
         side.wait_event(ev)
@@ -141,11 +166,23 @@ def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, l
                                       _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))
 
 
+def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo):
+    ws = _workspace(C.device)
+    _lib.check(_lib.lib().grappa_gemm_actgrad(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(elu_out), ld_eo, MATH_MODE,
+                                              _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))
+
+
 class LinearFn(torch.autograd.Function):
-    """y = dropout(act(x W^T + b)) + res1 + res2, columns padded to `out_ld` (pad columns are zero)."""
+    """y = dropout(act(x W^T + b)) + res1 + res2, columns padded to `out_ld` (pad columns are zero).
+
+    Two flags let a Linear-ELU-Linear block skip the elementwise ELU backward pass over its hidden tensor:
+      x_is_elu_out  (second layer): x is the plain ELU output of the preceding layer and feeds nothing else, so the
+                    backward returns dL/d(pre-activation of that layer) -- ELU' is fused into the dX GEMM epilogue;
+      grad_is_preact (first layer, act = ELU, no dropout / residual): the incoming gradient is already w.r.t. the
+                    pre-activation."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld):
+    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out=False, grad_is_preact=False):
         x, lda = _rows2d(x, "x")
         w, ldb = _rows2d(weight, "weight")
         M, K = x.shape
@@ -167,7 +204,10 @@ class LinearFn(torch.autograd.Function):
         gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev)
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
                               r2 if act != ACT_NONE else None)
+        if grad_is_preact and (act != ACT_ELU or drop_p > 0 or res1 is not None or res2 is not None):
+            raise ValueError("grad_is_preact needs a plain ELU layer (no dropout, no residual)")
         ctx.cfg = (act, float(drop_p), seed, seed_dev, N, ldc, bias is not None, res1 is not None, res2 is not None)
+        ctx.flags = (bool(x_is_elu_out), bool(grad_is_preact))
         ctx.sink_ids = (id(weight), id(bias))
         return y
 
@@ -175,6 +215,9 @@ class LinearFn(torch.autograd.Function):
     def backward(ctx, dy):
         x, w, y, r1, r2 = ctx.saved_tensors
         act, drop_p, seed, seed_dev, N, ldc, has_bias, has_r1, has_r2 = ctx.cfg
+        x_is_elu_out, grad_is_preact = ctx.flags
+        if grad_is_preact:
+            act = ACT_NONE                   # dy already is dL/d(pre-activation): the next layer's dX GEMM applied ELU'
         L = _lib.lib()
         dy, lddy = _rows2d(dy, "grad")
         M, K = x.shape
@@ -219,16 +262,27 @@ class LinearFn(torch.autograd.Function):
             param_grads()
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
-            gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
+            if x_is_elu_out:
+                gemm_actgrad(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, x, lda)
+            else:
+                gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
         if b_sunk:
             db = None
         dr = dy if ldc == N else dy[:, :N]
         return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,
-                dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None)
+                dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None, None, None)
 
 
-def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0):
-    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld)
+def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0, x_is_elu_out=False,
+           grad_is_preact=False):
+    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact)
+
+
+def elu_mlp(x, w1, b1, w2, b2, act2=ACT_NONE, res1=None, res2=None, drop_p=0.0):
+    """Linear-ELU-Linear with the hidden tensor's ELU backward fused into the second layer's dX GEMM."""
+    fuse = FUSE_ELU_GRAD and torch.is_grad_enabled()
+    z = linear(x, w1, b1, act=ACT_ELU, grad_is_preact=fuse)
+    return linear(z, w2, b2, act=act2, res1=res1, res2=res2, drop_p=drop_p, x_is_elu_out=fuse)
 
 
 class LayerNormFn(torch.autograd.Function):

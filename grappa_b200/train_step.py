@@ -165,8 +165,7 @@ class TrainStep:
         if _model.PARALLEL_WRITERS:
             for wst in _model._writer_streams(self.device):
                 comm.wait_stream(wst)
-        side = ops._SIDE_STREAMS.get(self.device)
-        if side is not None:
+        for side in ops.side_streams(self.device):
             comm.wait_stream(side)
 
     def _state_for(self, packed: PackedBatch):

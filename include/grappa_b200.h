@@ -49,6 +49,16 @@ int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
                 float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
                 float* workspace, int64_t workspace_floats, void* stream);
 
+/* Backward GEMM with the activation derivative fused into its epilogue: C = (A op B) * ELU'(pre-activation), the
+ * derivative read off the saved ELU OUTPUT s (ELU'(x) = 1 for x > 0, else exp(x) = s + 1).  Used for dL/d(pre) of the
+ * first layer of every Linear-ELU-Linear block (network_utils.py:44-54, graph_attention.py:304-317), where autograd in
+ * the reference runs a separate elementwise ELU backward over the (rows, hidden) tensor.  Layouts, math_mode and
+ * workspace as grappa_gemm; elu_out: (M, N) with leading dimension ld_eo. */
+int grappa_gemm_actgrad(int layout, int64_t M, int64_t N, int64_t K,
+                        const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                        const float* elu_out, int64_t ld_eo, int math_mode,
+                        float* workspace, int64_t workspace_floats, void* stream);
+
 /* dZ = dY * keepmask/(1-p) * act'(.) where the activation output is recovered as (Y - res1 - res2)*(1-p).
  * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL.
  * colsum_out (N, may be NULL): also returns sum_m dZ[m,:] (the bias gradient) from the same pass; needs scratch of

@@ -373,3 +373,32 @@ def test_pe_table_and_row_gather_ops():
     (X * w).sum().backward()
     ref = torch.zeros_like(tab).index_add_(0, rows, w)
     torch.testing.assert_close(tab.grad, ref, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("M,H,act2", [(300, 256, 0), (1280, 2048, 1), (77, 100, 0), (4096, 2048, 0)])
+def test_elu_mlp_fused_activation_gradient(M, H, act2, monkeypatch):
+    """Linear-ELU-Linear with ELU' fused into the second layer's dX GEMM epilogue (grappa_gemm_actgrad) against the
+    unfused path and against PyTorch: interior and edge tiles, split-K and FFMA fallbacks included via the shapes."""
+    torch.manual_seed(M + H)
+    D = 512 if H >= 256 else 52
+    x = torch.randn(M, D, device=DEV)
+    w1, b1 = torch.randn(H, D, device=DEV) / math.sqrt(D), torch.randn(H, device=DEV) * 0.1
+    w2, b2 = torch.randn(D, H, device=DEV) / math.sqrt(H), torch.randn(D, device=DEV) * 0.1
+    gout = torch.randn(M, D, device=DEV)
+    res = {}
+    for mode in ("fused", "unfused", "torch"):
+        leaves = [t.clone().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+        if mode == "torch":
+            z = F.elu(leaves[0] @ leaves[1].T + leaves[2])
+            y = z @ leaves[3].T + leaves[4]
+            y = F.elu(y) if act2 else y
+            y = y + leaves[0]
+        else:
+            monkeypatch.setattr(ops, "FUSE_ELU_GRAD", mode == "fused")
+            y = ops.elu_mlp(leaves[0], leaves[1], leaves[2], leaves[3], leaves[4], act2=act2, res1=leaves[0])
+        y.backward(gout)
+        res[mode] = [y.detach()] + [t.grad for t in leaves]
+    for a, b, c in zip(res["fused"], res["unfused"], res["torch"]):
+        scale = float(c.abs().max()) + 1e-12
+        assert float((a - b).abs().max()) / scale < 2e-6
+        assert float((a - c).abs().max()) / scale < 2e-5
