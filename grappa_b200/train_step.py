@@ -43,6 +43,15 @@ class _BucketBoundary(torch.autograd.Function):
         return grad, None
 
 
+class _LossHandle:
+    def __init__(self, buf, ev):
+        self._buf, self._ev = buf, ev
+
+    def value(self) -> float:
+        self._ev.synchronize()
+        return float(self._buf[0])
+
+
 class FlatParameters:
     def __init__(self, model: torch.nn.Module, device):
         self.named = [(n, p) for n, p in model.named_parameters() if p.requires_grad and not any(u in n for u in _UNUSED)]
@@ -98,6 +107,9 @@ class TrainStep:
         if self.overlap_comm and world_size > 1:
             raise NotImplementedError("overlap_comm with NCCL hung on 2 x B200 in round 1; use the default single all-reduce")
         self._comm_stream = torch.cuda.Stream(device=self.device)
+        self._copy_stream = torch.cuda.Stream(device=self.device)        # input prefetch (H2D of the next step's batch)
+        self._loss_host = [torch.zeros(1).pin_memory() if torch.cuda.is_available() else torch.zeros(1) for _ in range(4)]
+        self._loss_slot = 0
         self._works = []
         self._reduce_fn = None            # test hook: replaces the NCCL all-reduce of one bucket
         first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
@@ -175,11 +187,53 @@ class TrainStep:
             self._static[packed.signature] = st
         return st
 
+    # ---- input pipelining ---------------------------------------------------------------------------------------------
+    def prefetch(self, packed: PackedBatch):
+        """Starts the host->device copy of a FUTURE step's inputs on the copy stream, into staging buffers, so that it
+        overlaps the step that is currently running; the step that consumes it only does a device-to-device copy into
+        the static buffers of the captured graph."""
+        st = self._state_for(packed)
+        stg = st.get("staging")
+        if stg is None:
+            stg = st["staging"] = {"f": torch.empty_like(st["batch"].fbuf), "i": torch.empty_like(st["batch"].ibuf),
+                                   "ready": torch.cuda.Event(), "free": None}
+        cs = self._copy_stream
+        if stg["free"] is not None:
+            cs.wait_event(stg["free"])               # the previous consumer has copied the staging buffers out
+        with torch.cuda.stream(cs):
+            stg["f"].copy_(packed.fbuf, non_blocking=True)
+            stg["i"].copy_(packed.plan.host, non_blocking=True)
+            stg["ready"].record(cs)
+        st["prefetched"] = packed
+
+    def _load(self, st, packed):
+        stg = st.get("staging")
+        if stg is not None and st.get("prefetched") is packed:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(stg["ready"])
+            st["batch"].fbuf.copy_(stg["f"], non_blocking=True)
+            st["batch"].ibuf.copy_(stg["i"], non_blocking=True)
+            stg["free"] = torch.cuda.Event()
+            stg["free"].record(cur)
+            st["prefetched"] = None
+        else:
+            st["batch"].load(packed)
+
+    def read_loss_async(self, loss: torch.Tensor):
+        """Device->host read of a step's loss without stalling the launch of the next step: returns a handle whose
+        `.value()` waits for (only) that copy."""
+        buf = self._loss_host[self._loss_slot % len(self._loss_host)]
+        self._loss_slot += 1
+        buf.copy_(loss.reshape(1), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        return _LossHandle(buf, ev)
+
     def compute_gradients(self, packed: PackedBatch, load: bool = True) -> torch.Tensor:
         """H2D (optional) + forward + loss + backward into the flat gradient buffer.  Returns the device loss."""
         st = self._state_for(packed)
         if load:
-            st["batch"].load(packed)
+            self._load(st, packed)
         g = st["batch"].graph
         if not self.use_cuda_graph:
             return self._fwd_bwd(g)

@@ -352,3 +352,36 @@ def test_drop_in_on_a_dgl_style_graph_object(golden_dir):
             assert torch.equal(v, graph_params(b)[lvl][key]), f"{lvl} {key}"
     assert torch.equal(a.nodes["g"].data["energy"], b.nodes["g"].data["energy"])
     assert torch.equal(a.nodes["n1"].data["gradient"], b.nodes["n1"].data["gradient"])
+
+
+def test_input_prefetch_and_async_loss_read_match_the_plain_step():
+    """TrainStep.prefetch (H2D of the next batch on a copy stream into staging buffers) + read_loss_async give the same
+    losses and weights as loading synchronously, with two different batches alternating."""
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.train_step import TrainStep
+    batches = [PackedBatch(batch([S.trimer_molecule(seed=s + 10 * b, n_confs=4) for s in range(3)])) for b in range(2)]
+    outs = []
+    for pipelined in (False, True):
+        model, _ = build_model(train=True)
+        ops.DropoutSeeds.manual_seed(99)
+        ts = TrainStep(model, DEV, use_cuda_graph=True)
+        losses = []
+        if pipelined:
+            ts.prefetch(batches[0])
+            pending = None
+            for k in range(6):
+                loss = ts.step(batches[k % 2])
+                if k + 1 < 6:
+                    ts.prefetch(batches[(k + 1) % 2])
+                h = ts.read_loss_async(loss)
+                if pending is not None:
+                    losses.append(pending.value())
+                pending = h
+            losses.append(pending.value())
+        else:
+            for k in range(6):
+                losses.append(float(ts.step(batches[k % 2])))
+        torch.cuda.synchronize()
+        outs.append((losses, ts.flat.params.clone()))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1], outs[1][1])
