@@ -290,6 +290,7 @@ def main():
         line["roofline"] = {"kernel": ("gemm_tc_kernel" if ops.MATH_MODE == 1 else "sgemm_kernel") +
                                       " (grappa_gemm: all dense layers fwd+bwd, fused bias/ELU/dropout/residual epilogue)",
                             "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                            "frac_of_3xtf32_ceiling": tf / (peak_tf / 6.0),
                             "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
                             "pipe": "fp32 FFMA (math_mode 0)" if ops.MATH_MODE == 0 else
                                     "tcgen05 kind::tf32, 3 MMAs per product (3xTF32): the pipe's own dense peak is 1/2 of bf16, "
