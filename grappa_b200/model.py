@@ -59,13 +59,17 @@ _WRITER_STREAMS = {}
 # distinct (atom, pe) row instead of once per token whenever there are at least DEDUP_RATIO times more tokens than rows.
 DEDUP_TOKENS = True
 DEDUP_RATIO = 1.5
+WRITER_STREAM_PRIORITIES = (-1, -1, -2, -1)
 
 
 def _writer_streams(device):
     device = ops.norm_device(device)
     st = _WRITER_STREAMS.get(device)
     if st is None:
-        st = [torch.cuda.Stream(device=device) for _ in range(4)]
+        # order: bond, angle, proper, improper.  Priorities (0 = lowest): the writers' chains sit above the side streams that
+        # carry parameter-gradient work (priority 0), the proper-torsion writer (most tokens, longest chain) above the
+        # rest.  Measured on the cfg-2 step: 4.35 -> 4.11 ms.
+        st = [torch.cuda.Stream(device=device, priority=p) for p in WRITER_STREAM_PRIORITIES]
         _WRITER_STREAMS[device] = st
     return st
 

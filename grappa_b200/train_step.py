@@ -119,7 +119,8 @@ class TrainStep:
         self._static: Dict[tuple, dict] = {}
         # warm-up and capture both run on this side stream (the whole-network capture recipe of torch.cuda.graphs:
         # autograd's per-stream state must exist before capture begins)
-        self._side = torch.cuda.Stream(device=self.device) if use_cuda_graph else None
+        # priority -1: the activation-gradient chain goes ahead of the parameter-gradient side streams (priority 0)
+        self._side = torch.cuda.Stream(device=self.device, priority=-1) if use_cuda_graph else None
 
     # ---- one forward + loss + backward on device-resident inputs -------------------------------------------------
     def _fwd_bwd(self, g):
