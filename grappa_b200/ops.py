@@ -36,7 +36,7 @@ def norm_device(device) -> torch.device:
 
 
 SIDE_STREAM_PER_STREAM = _os.environ.get("GRAPPA_SIDE_PER_STREAM", "1") != "0"
-SIDE_POOL = int(_os.environ.get("GRAPPA_SIDE_POOL", "1"))      # side streams per compute stream, used round-robin
+SIDE_POOL = int(_os.environ.get("GRAPPA_SIDE_POOL", "2"))      # side streams per compute stream, used round-robin (measured: 1 -> 2: -1.5 %)
 _SIDE_RR = {}
 
 
