@@ -385,3 +385,21 @@ def test_input_prefetch_and_async_loss_read_match_the_plain_step():
         outs.append((losses, ts.flat.params.clone()))
     assert outs[0][0] == outs[1][0]
     assert torch.equal(outs[0][1], outs[1][1])
+
+
+def test_split_update_under_the_next_gnn_forward_is_bit_identical():
+    """TrainStep(split_update=True) updates the writers' parameters on an update stream while the next step's GNN forward
+    runs (an external-event wait node in the captured graph guards the writers): same losses, same weights."""
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.train_step import TrainStep
+    packed = PackedBatch(batch([S.trimer_molecule(seed=s, n_confs=4) for s in range(3)]))
+    outs = []
+    for split in (False, True):
+        model, _ = build_model(train=True)
+        ops.DropoutSeeds.manual_seed(7)
+        ts = TrainStep(model, DEV, use_cuda_graph=True, split_update=split)
+        losses = [float(ts.step(packed)) for _ in range(7)]
+        ts.synchronize()
+        outs.append((losses, ts.flat.params.clone(), ts.flat.exp_avg_sq.clone()))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
