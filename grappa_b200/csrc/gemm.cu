@@ -236,6 +236,8 @@ static int gemm_impl(int layout, int64_t M, int64_t N, int64_t K,
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldr1 = ldr1; p.ldr2 = ldr2;
     p.act = act; p.drop_p = drop_p; p.drop_scale = 1.0f / (1.0f - drop_p); p.seed = seed; p.seed_dev = seed_dev;
     p.elu_out = elu_out; p.ld_eo = ld_eo;
+    p.cta_budget = (math_mode >> 8) & 0xFF;     // optional: bits 8..15 of math_mode carry the CTA budget of a background GEMM
+    math_mode &= 0xFF;
     p.a_vec = aligned16(A) && (lda % 4 == 0);
     p.b_vec = aligned16(B) && (ldb % 4 == 0);
     p.c_vec = aligned16(C) && (ldc % 4 == 0);

@@ -13,6 +13,8 @@ struct GemmParams {
     // optional last epilogue step (backward GEMMs): C *= ELU'(pre-activation) read off the saved ELU OUTPUT s:
     // ELU'(x) = 1 for x > 0, exp(x) = s + 1 otherwise
     const float* elu_out = nullptr; int64_t ld_eo = 0;
+    int cta_budget = 0;        // > 0: background GEMM (weight gradients on a side stream): split-K grids are sized for this
+                               // many CTAs instead of the whole machine, so that the critical chain always finds free SMs
 };
 
 __device__ __forceinline__ float elu_grad_from_out(float s) { return s > 0.f ? 1.f : s + 1.f; }

@@ -648,8 +648,9 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams
     // extra pass; slices are multiples of the promotion chunk.  tiles * splits stays <= 148 (one CTA per SM): one CTA
     // more than that costs a whole second wave (measured: 40 tiles x 4 slices = 160 CTAs 42 us, x 3 slices 29 us).
     int splits = 1;
-    if (workspace != nullptr && tiles <= 74 && nk >= 32) {
-        const int want = (int)std::min<int64_t>(148 / tiles, nk / 16);
+    const int64_t budget = p.cta_budget > 0 ? p.cta_budget : 148;
+    if (workspace != nullptr && tiles <= budget / 2 && nk >= 32) {
+        const int want = (int)std::min<int64_t>(budget / tiles, nk / 16);
         if (want > 1 && (int64_t)want * p.M * p.N <= workspace_floats) splits = want;
     }
     int kps = nk;

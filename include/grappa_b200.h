@@ -39,7 +39,10 @@ int64_t grappa_launch_count(void);
  * act: 0 none, 1 ELU(alpha=1).  bias (N) / res1 / res2 may be NULL.  drop_p in [0,1): keep-mask from a
  * counter-based hash of (seed + *seed_dev, row*N+col), kept values scaled by 1/(1-p).  seed_dev (device, may be
  * NULL) lets a captured CUDA graph draw fresh masks on every replay: the step driver bumps it between steps.
- * math_mode: 0 = fp32 FFMA tiles, 1 = tcgen05 3xTF32 (split-precision tensor-core tiles, fp32-level accuracy).
+ * math_mode: low byte 0 = fp32 FFMA tiles, 1 = tcgen05 3xTF32 (split-precision tensor-core tiles, fp32-level accuracy);
+ *            bits 8..15 (optional, 0 = unset): CTA budget of a BACKGROUND GEMM (weight gradients issued on a side
+ *            stream): its split-K grid is sized for that many CTAs instead of all 148 SMs, so that the kernels of the
+ *            critical chain always find free SMs.
  * workspace (may be NULL): caller-provided scratch of workspace_floats floats; lets the tensor-core path split the k
  * range over several CTAs when the output has few tiles (weight gradients), reduced in fixed order.
  */
