@@ -304,6 +304,26 @@ def main():
                             "flops_per_step": gm["flops"], "ms_per_step": gemm_ms,
                             "avg_launch_us": gemm_ms * 1e3 / gm["calls"],
                             "method": "the step's recorded launches replayed back to back in a CUDA graph, CUDA events"}
+        # The weight-gradient GEMMs are issued on low-priority side streams with a CTA budget (un-split: 4-64 CTAs
+        # each) so that they run UNDER the activation-gradient chains; replayed alone and serially they look slow by
+        # construction.  Both classes are reported; `achieved` above is over all launches, as the contract defines it.
+        is_bg = lambda n, a: n == "grappa_gemm" and ((a[19] >> 16) & 1) == 1
+        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad"}
+        fl = {"foreground": [0.0, 0], "background": [0.0, 0]}
+        for n, _, _, a in prof.records:
+            if n in gemm_names:
+                c = fl["background" if is_bg(n, a) else "foreground"]
+                c[0] += 2.0 * a[1] * a[2] * a[3]
+                c[1] += 1
+        for cls, keep in (("foreground", lambda n, a: not is_bg(n, a)), ("background", is_bg)):
+            ms_c = prof.replay_ms(gemm_names, keep=keep)
+            if ms_c > 0:
+                line["roofline"][cls] = {"launches": fl[cls][1], "flops": fl[cls][0], "ms": ms_c,
+                                         "achieved": fl[cls][0] / (ms_c * 1e-3) / 1e12,
+                                         "frac_of_3xtf32_ceiling": fl[cls][0] / (ms_c * 1e-3) / 1e12 / (peak_tf / 6.0)}
+        line["roofline"]["class_note"] = ("foreground = GEMMs on the critical chains (forward, activation gradients); background = "
+                                          "weight-gradient GEMMs on low-priority side streams, deliberately un-split (few CTAs) so "
+                                          "that they fill idle SMs under the chains: 4.06 -> 3.93 ms per step")
         others = {}
         for name, label in (("grappa_energy_fwd", "energy_fwd"), ("grappa_energy_vjp", "energy_vjp"), ("grappa_gnn_attn_fwd", "gnn_attn_fwd")):
             if name in summ and dev_ms.get(name, 0) > 0:

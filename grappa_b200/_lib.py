@@ -92,14 +92,14 @@ class Profiler:
         return out
 
 
-    def replay_ms(self, names, iters: int = 5) -> float:
+    def replay_ms(self, names, iters: int = 5, keep=None) -> float:
         """Re-issues the recorded calls of the given entry points (same arguments, same buffers) inside ONE CUDA graph
         and times its replay with CUDA events: back-to-back device time of those kernels, free of host launch gaps.
         The recorded buffers may have been recycled by the allocator; they are still mapped, which is all timing needs."""
         import ctypes
         import torch
         raw = _raw_lib()
-        calls = [(getattr(raw, n), args) for n, _, _, args in self.records if n in names]
+        calls = [(getattr(raw, n), args) for n, _, _, args in self.records if n in names and (keep is None or keep(n, args))]
         if not calls:
             return 0.0
         torch.cuda.synchronize()

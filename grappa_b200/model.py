@@ -70,6 +70,7 @@ def _writer_streams(device):
         # carry parameter-gradient work (priority 0), the proper-torsion writer (most tokens, longest chain) above the
         # rest.  Measured on the cfg-2 step: 4.35 -> 4.11 ms.
         st = [torch.cuda.Stream(device=device, priority=p) for p in WRITER_STREAM_PRIORITIES]
+        ops.THROUGHPUT_STREAMS.update(x.cuda_stream for x in st)
         _WRITER_STREAMS[device] = st
     return st
 

@@ -166,12 +166,19 @@ def _workspace(device):
 # pass.  Measured on the cfg-2 step: 4.06 -> 3.93 ms.
 SIDE_CTA_BUDGET = int(_os.environ.get("GRAPPA_SIDE_CTA_BUDGET", "8"))
 _IN_SIDE = [0]
+# streams on which the machine is saturated by several concurrent chains (the four writers): split-K there trades SM time
+# for latency, which does not pay when throughput is the limit
+WRITER_CTA_BUDGET = int(_os.environ.get("GRAPPA_WRITER_CTA_BUDGET", "8"))       # measured: 3.915 -> 3.893 ms
+THROUGHPUT_STREAMS = set()
 
 
 def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
          drop_p=0.0, seed=0, seed_dev=None):
     ws = _workspace(C.device)
-    mode = MATH_MODE | ((SIDE_CTA_BUDGET << 8) if _IN_SIDE[0] else 0)
+    budget = SIDE_CTA_BUDGET if _IN_SIDE[0] else 0
+    if not budget and WRITER_CTA_BUDGET and torch.cuda.current_stream().cuda_stream in THROUGHPUT_STREAMS:
+        budget = WRITER_CTA_BUDGET
+    mode = MATH_MODE | (budget << 8) | (0x10000 if _IN_SIDE[0] else 0)     # bit 16: bookkeeping only (ignored by the library)
     _lib.check(_lib.lib().grappa_gemm(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act,
                                       _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), mode,
                                       _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))

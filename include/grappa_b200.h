@@ -42,7 +42,7 @@ int64_t grappa_launch_count(void);
  * math_mode: low byte 0 = fp32 FFMA tiles, 1 = tcgen05 3xTF32 (split-precision tensor-core tiles, fp32-level accuracy);
  *            bits 8..15 (optional, 0 = unset): CTA budget of a BACKGROUND GEMM (weight gradients issued on a side
  *            stream): its split-K grid is sized for that many CTAs instead of all 148 SMs, so that the kernels of the
- *            critical chain always find free SMs.
+ *            critical chain always find free SMs.  Higher bits are ignored (callers may use them for bookkeeping).
  * workspace (may be NULL): caller-provided scratch of workspace_floats floats; lets the tensor-core path split the k
  * range over several CTAs when the output has few tiles (weight gradients), reduced in fixed order.
  */
