@@ -82,7 +82,8 @@ class TrainStep:
     def __init__(self, model, device, lr: float = 1e-5, weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8,
                  energy_weight: float = 1.0, gradient_weight: float = 0.8, proper_regularisation: float = 1.0,
                  improper_regularisation: float = 1.0, world_size: int = 1, use_cuda_graph: bool = True,
-                 process_group=None, overlap_comm: Optional[bool] = None, split_update: Optional[bool] = None):
+                 process_group=None, overlap_comm: Optional[bool] = None, split_update: Optional[bool] = None,
+                 max_cached_shapes: int = 8):
         self.device = ops.norm_device(device)
         self.model = model.to(self.device).train()
         self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
@@ -125,7 +126,10 @@ class TrainStep:
         self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
         assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
         self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
+        # static device buffers + captured graph per batch SHAPE (signature), least recently used first.  Real datasets
+        # have many shapes: only `max_cached_shapes` stay resident (each holds its activations' memory pool).
         self._static: Dict[tuple, dict] = {}
+        self.max_cached_shapes = max_cached_shapes
         # warm-up and capture both run on this side stream (the whole-network capture recipe of torch.cuda.graphs:
         # autograd's per-stream state must exist before capture begins)
         # priority -1: the activation-gradient chain goes ahead of the parameter-gradient side streams (priority 0)
@@ -196,10 +200,16 @@ class TrainStep:
             comm.wait_stream(side)
 
     def _state_for(self, packed: PackedBatch):
-        st = self._static.get(packed.signature)
+        sig = packed.signature
+        st = self._static.pop(sig, None)
         if st is None:
+            while len(self._static) >= max(1, self.max_cached_shapes):        # evict the least recently used shape
+                old = self._static.pop(next(iter(self._static)))
+                if old.get("graph") is not None or old.get("staging") is not None:
+                    torch.cuda.synchronize(self.device)                        # nothing of it may still be in flight
+                old.clear()
             st = {"batch": DeviceBatch(packed, self.device), "graph": None, "loss": None, "warm": 0}
-            self._static[packed.signature] = st
+        self._static[sig] = st                                                 # most recently used last
         return st
 
     # ---- input pipelining ---------------------------------------------------------------------------------------------

@@ -403,3 +403,20 @@ def test_split_update_under_the_next_gnn_forward_is_bit_identical():
         outs.append((losses, ts.flat.params.clone(), ts.flat.exp_avg_sq.clone()))
     assert outs[0][0] == outs[1][0]
     assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][2], outs[1][2])
+
+
+def test_shape_cache_is_bounded_and_evicted_shapes_still_train():
+    """One static buffer set + captured graph per batch shape, least recently used evicted beyond `max_cached_shapes`;
+    a shape that comes back after eviction is simply warmed up and captured again."""
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.train_step import TrainStep
+    shapes = [PackedBatch(batch([S.trimer_molecule(seed=s, n_confs=c) for s in range(n)])) for n, c in ((2, 3), (3, 3), (2, 5))]
+    model, _ = build_model(train=True)
+    ts = TrainStep(model, DEV, use_cuda_graph=True, max_cached_shapes=2)
+    for rnd in range(2):
+        for pk in shapes:
+            for _ in range(5):                      # 3 warm-ups, capture, replay
+                loss = ts.step(pk)
+            assert torch.isfinite(loss)
+            assert len(ts._static) <= 2
+    assert shapes[0].signature not in ts._static and shapes[2].signature in ts._static
