@@ -278,12 +278,15 @@ def main():
         _lib.profiler = None
         ts.use_cuda_graph = ts_graph
         # device time per entry point: its recorded launches replayed back to back in one CUDA graph (CUDA events)
-        if "grappa_gemm_actgrad" in summ:              # same kernel, backward epilogue variant: one roofline entry
-            extra_g = summ.pop("grappa_gemm_actgrad")
-            for k2 in ("calls", "ms", "flops"):
-                summ["grappa_gemm"][k2] += extra_g[k2]
+        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex"}     # one kernel family: one roofline entry
+        summ.setdefault("grappa_gemm", {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+        for other in ("grappa_gemm_actgrad", "grappa_gemm_ex"):
+            if other in summ:
+                extra_g = summ.pop(other)
+                for k2 in ("calls", "ms", "flops"):
+                    summ["grappa_gemm"][k2] += extra_g[k2]
         names = sorted(summ.keys())
-        dev_ms = {n: prof.replay_ms({n, "grappa_gemm_actgrad"} if n == "grappa_gemm" else {n}) for n in names}
+        dev_ms = {n: prof.replay_ms(gemm_names if n == "grappa_gemm" else {n}) for n in names}
         tot = sum(dev_ms.values())
         step_ms = ms / K
         gm = summ["grappa_gemm"]
@@ -307,8 +310,7 @@ def main():
         # The weight-gradient GEMMs are issued on low-priority side streams with a CTA budget (un-split: 4-64 CTAs
         # each) so that they run UNDER the activation-gradient chains; replayed alone and serially they look slow by
         # construction.  Both classes are reported; `achieved` above is over all launches, as the contract defines it.
-        is_bg = lambda n, a: n == "grappa_gemm" and ((a[19] >> 16) & 1) == 1
-        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad"}
+        is_bg = lambda n, a: n in ("grappa_gemm", "grappa_gemm_ex") and ((a[19] >> 16) & 1) == 1
         fl = {"foreground": [0.0, 0], "background": [0.0, 0]}
         for n, _, _, a in prof.records:
             if n in gemm_names:

@@ -21,6 +21,8 @@ PROTOTYPES = {
     "grappa_launch_count": (I64, []),
     "grappa_gemm": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P]),
     "grappa_gemm_actgrad": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I64, I, P, I64, P]),
+    "grappa_gemm_ex": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P, P]),
+    "grappa_split_lo": (I, [I64, P, P, P]),
     "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P, P, P]),
     "grappa_colsum_scratch_floats": (I64, [I64, I64]),
     "grappa_colsum": (I, [I64, I64, P, I64, P, P, P]),
@@ -81,7 +83,7 @@ class Profiler:
             d = out.setdefault(name, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
             d["calls"] += 1
             d["ms"] += a.elapsed_time(b)
-            if name in ("grappa_gemm", "grappa_gemm_actgrad"):
+            if name in ("grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex"):
                 d["flops"] += 2.0 * args[1] * args[2] * args[3]
             elif name == "grappa_energy_fwd":                      # 24 B per atom-conformation + 20 B per molecule-conformation
                 d["bytes"] += args[2] * (24.0 * args[0] + 20.0 * args[1])

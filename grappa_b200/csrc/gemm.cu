@@ -223,7 +223,7 @@ static int gemm_impl(int layout, int64_t M, int64_t N, int64_t K,
                            const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
                            float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
                            float* workspace, int64_t workspace_floats, void* stream,
-                           const float* elu_out, int64_t ld_eo) {
+                           const float* elu_out, int64_t ld_eo, const float* B_lo = nullptr) {
     GRAPPA_CHECK_ARG(layout >= 0 && layout <= 2, "layout must be 0 (NT), 1 (NN) or 2 (TN)");
     GRAPPA_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "negative size");
     GRAPPA_CHECK_ARG(act == 0 || act == 1, "act must be 0 (none) or 1 (ELU)");
@@ -235,7 +235,7 @@ static int gemm_impl(int layout, int64_t M, int64_t N, int64_t K,
     p.A = A; p.B = B; p.C = C; p.bias = bias; p.res1 = res1; p.res2 = res2;
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.ldr1 = ldr1; p.ldr2 = ldr2;
     p.act = act; p.drop_p = drop_p; p.drop_scale = 1.0f / (1.0f - drop_p); p.seed = seed; p.seed_dev = seed_dev;
-    p.elu_out = elu_out; p.ld_eo = ld_eo;
+    p.elu_out = elu_out; p.ld_eo = ld_eo; p.B_lo = B_lo;
     p.cta_budget = (math_mode >> 8) & 0xFF;     // optional: bits 8..15 of math_mode carry the CTA budget of a background GEMM
     math_mode &= 0xFF;
     p.a_vec = aligned16(A) && (lda % 4 == 0);
@@ -270,4 +270,15 @@ extern "C" int grappa_gemm_actgrad(int layout, int64_t M, int64_t N, int64_t K,
     GRAPPA_CHECK_ARG(elu_out != nullptr && ld_eo >= N, "elu_out (M, N) with ld_eo >= N is required");
     return gemm_impl(layout, M, N, K, A, lda, B, ldb, C, ldc, nullptr, 0, nullptr, 0, nullptr, 0, 0.f, 0, nullptr, math_mode,
                      workspace, workspace_floats, stream, elu_out, ld_eo);
+}
+
+extern "C" int grappa_gemm_ex(int layout, int64_t M, int64_t N, int64_t K,
+                              const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                              const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                              float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                              float* workspace, int64_t workspace_floats,
+                              const float* elu_out, int64_t ld_eo, const float* B_lo, void* stream) {
+    GRAPPA_CHECK_ARG(elu_out == nullptr || ld_eo >= N, "ld_eo must be >= N");
+    return gemm_impl(layout, M, N, K, A, lda, B, ldb, C, ldc, bias, act, res1, ldr1, res2, ldr2, drop_p, seed, seed_dev, math_mode,
+                     workspace, workspace_floats, stream, elu_out, ld_eo, B_lo);
 }

@@ -13,6 +13,7 @@ struct GemmParams {
     // optional last epilogue step (backward GEMMs): C *= ELU'(pre-activation) read off the saved ELU OUTPUT s:
     // ELU'(x) = 1 for x > 0, exp(x) = s + 1 otherwise
     const float* elu_out = nullptr; int64_t ld_eo = 0;
+    const float* B_lo = nullptr;   // optional pre-split lo plane of B (same shape / ldb): see gemm_tc.cu B_PRE
     int cta_budget = 0;        // > 0: background GEMM (weight gradients on a side stream): split-K grids are sized for this
                                // many CTAs instead of the whole machine, so that the critical chain always finds free SMs
 };

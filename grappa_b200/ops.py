@@ -172,22 +172,61 @@ WRITER_CTA_BUDGET = int(_os.environ.get("GRAPPA_WRITER_CTA_BUDGET", "8"))       
 THROUGHPUT_STREAMS = set()
 
 
-def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
-         drop_p=0.0, seed=0, seed_dev=None):
-    ws = _workspace(C.device)
+def _gemm_mode():
     budget = SIDE_CTA_BUDGET if _IN_SIDE[0] else 0
     if not budget and WRITER_CTA_BUDGET and torch.cuda.current_stream().cuda_stream in THROUGHPUT_STREAMS:
         budget = WRITER_CTA_BUDGET
-    mode = MATH_MODE | (budget << 8) | (0x10000 if _IN_SIDE[0] else 0)     # bit 16: bookkeeping only (ignored by the library)
-    _lib.check(_lib.lib().grappa_gemm(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act,
-                                      _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), mode,
-                                      _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))
+    return MATH_MODE | (budget << 8) | (0x10000 if _IN_SIDE[0] else 0)     # bit 16: bookkeeping only (ignored by the library)
 
 
-def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo):
+def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
+         drop_p=0.0, seed=0, seed_dev=None, elu_out=None, ld_eo=0, b_lo=None):
     ws = _workspace(C.device)
-    _lib.check(_lib.lib().grappa_gemm_actgrad(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(elu_out), ld_eo, MATH_MODE,
-                                              _p(ws), WORKSPACE_FLOATS if ws is not None else 0, _stream()))
+    wsf = WORKSPACE_FLOATS if ws is not None else 0
+    L = _lib.lib()
+    if elu_out is None and b_lo is None:
+        _lib.check(L.grappa_gemm(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act, _p(res1), ldr1, _p(res2), ldr2,
+                                 float(drop_p), seed, _p(seed_dev), _gemm_mode(), _p(ws), wsf, _stream()))
+    else:
+        _lib.check(L.grappa_gemm_ex(layout, M, N, K, _p(A), lda, _p(B), ldb, _p(C), ldc, _p(bias), act, _p(res1), ldr1, _p(res2), ldr2,
+                                    float(drop_p), seed, _p(seed_dev), _gemm_mode(), _p(ws), wsf,
+                                    _p(elu_out), ld_eo, _p(b_lo), _stream()))
+
+
+# Pre-split weights (see grappa_gemm_ex / grappa_split_lo): {id(parameter): lo plane}.  The training-step driver keeps a
+# flat lo buffer next to its flat parameter buffer and refreshes it after every AdamW launch; without a driver (inference)
+# lo planes are made on first use and cached per weight version.
+WEIGHT_LO = None
+USE_WEIGHT_LO = _os.environ.get("GRAPPA_WEIGHT_LO", "1") != "0"
+_LO_CACHE = {}
+
+
+def split_lo(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    x = _req(x, "x").contiguous()
+    out = torch.empty_like(x) if out is None else out
+    _lib.check(_lib.lib().grappa_split_lo(x.numel(), _p(x), _p(out), _stream()))
+    return out
+
+
+def weight_lo(w: torch.Tensor):
+    """lo plane of a weight matrix for the B operand of the NT / NN GEMMs, or None."""
+    if not USE_WEIGHT_LO or MATH_MODE != 1 or w.dim() != 2 or w.shape[1] % 4 or w.shape[1] < 32 or w.shape[0] < 32 or not w.is_contiguous():
+        return None
+    if WEIGHT_LO is not None:
+        return WEIGHT_LO.get(id(w))
+    if torch.is_grad_enabled() and w.requires_grad:
+        return None                       # plain autograd use: weights change behind our back
+    key = id(w)
+    hit = _LO_CACHE.get(key)
+    if hit is not None and hit[0] == w._version and hit[1] == w.data_ptr():
+        return hit[2]
+    lo = split_lo(w.detach())
+    _LO_CACHE[key] = (w._version, w.data_ptr(), lo)
+    return lo
+
+
+def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo, b_lo=None):
+    gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out=elu_out, ld_eo=ld_eo, b_lo=b_lo)
 
 
 class LinearFn(torch.autograd.Function):
@@ -219,7 +258,9 @@ class LinearFn(torch.autograd.Function):
             r2, l2 = _rows2d(res2, "res2")
         seed = DropoutSeeds.next() if drop_p > 0 else 0
         seed_dev = DropoutSeeds.dev if drop_p > 0 else None
-        gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev)
+        w_lo = weight_lo(weight) if ldb == K else None
+        gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev, b_lo=w_lo)
+        ctx.w_lo = w_lo
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
                               r2 if act != ACT_NONE else None)
         if grad_is_preact and (act != ACT_ELU or drop_p > 0 or res1 is not None or res2 is not None):
@@ -281,9 +322,9 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
             if x_is_elu_out:
-                gemm_actgrad(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, x, lda)
+                gemm_actgrad(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, x, lda, b_lo=ctx.w_lo)
             else:
-                gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K)
+                gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, b_lo=ctx.w_lo)
         if b_sunk:
             db = None
         dr = dy if ldc == N else dy[:, :N]

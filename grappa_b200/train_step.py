@@ -65,6 +65,8 @@ class FlatParameters:
         self.grads = torch.zeros(total, device=device, dtype=torch.float32)
         self.exp_avg = torch.zeros(total, device=device, dtype=torch.float32)
         self.exp_avg_sq = torch.zeros(total, device=device, dtype=torch.float32)
+        self.params_lo = torch.zeros(total, device=device, dtype=torch.float32)     # lo planes of the pre-split weights
+        self.lo_of = {}
         self.sink = {}
         for n, p in self.named:
             o = self.offsets[n]
@@ -72,6 +74,7 @@ class FlatParameters:
             view.copy_(p.data)
             p.data = view
             self.sink[id(p)] = self.grads[o:o + p.numel()].view_as(p)
+            self.lo_of[id(p)] = self.params_lo[o:o + p.numel()].view_as(p)
 
     def grad_of(self, name: str) -> torch.Tensor:
         p = dict(self.named)[name]
@@ -88,6 +91,9 @@ class TrainStep:
         self.model = model.to(self.device).train()
         self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
         self.flat = FlatParameters(self.model, self.device)
+        if ops.USE_WEIGHT_LO:                                   # lo planes of the initial weights (refreshed after every AdamW)
+            _lib.check(_lib.lib().grappa_split_lo(self.flat.numel, ops._p(self.flat.params), ops._p(self.flat.params_lo),
+                                                  ops._stream()))
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         self.weights = (energy_weight, gradient_weight, proper_regularisation, improper_regularisation)
         self.world_size = world_size
@@ -138,6 +144,7 @@ class TrainStep:
     # ---- one forward + loss + backward on device-resident inputs -------------------------------------------------
     def _fwd_bwd(self, g):
         ops.GRAD_SINK = self.flat.sink
+        ops.WEIGHT_LO = self.flat.lo_of if ops.USE_WEIGHT_LO else None
         ops.DropoutSeeds.dev = self.seed_dev
         try:
             if self.overlap_comm:
@@ -174,6 +181,7 @@ class TrainStep:
             self.seed_dev.add_(1)
         finally:
             ops.GRAD_SINK = None
+            ops.WEIGHT_LO = None
             ops.DropoutSeeds.dev = None
         return loss.detach()
 
@@ -299,6 +307,8 @@ class TrainStep:
         _lib.check(_lib.lib().grappa_adamw(hi - lo, ptr(f.params), ptr(f.grads), ptr(f.exp_avg), ptr(f.exp_avg_sq),
                                            self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
                                            getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
+        if ops.USE_WEIGHT_LO:            # lo planes of the updated weights for the next step's GEMMs (B operand pre-split)
+            _lib.check(_lib.lib().grappa_split_lo(hi - lo, ptr(f.params), ptr(f.params_lo), ops._stream()))
 
     def exchange_and_update(self):
         """Gradient exchange + AdamW.  With `split_update` the GNN bucket goes first on the compute stream and the

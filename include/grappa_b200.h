@@ -62,6 +62,22 @@ int grappa_gemm_actgrad(int layout, int64_t M, int64_t N, int64_t K,
                         const float* elu_out, int64_t ld_eo, int math_mode,
                         float* workspace, int64_t workspace_floats, void* stream);
 
+/* Superset of the two entry points above.  elu_out / ld_eo as in grappa_gemm_actgrad (NULL: none).
+ * B_lo (NULL: none): pre-split low plane of the B operand, same shape and ldb as B, as written by grappa_split_lo.  For
+ * layouts 0 and 1 on the tensor-core path the kernel then TMA-loads B's lo tile instead of recomputing it in every CTA
+ * and k-block (B is a weight matrix there: split once per optimiser step); results are bit-identical.  Ignored by the
+ * FFMA path and for layout 2. */
+int grappa_gemm_ex(int layout, int64_t M, int64_t N, int64_t K,
+                   const float* A, int64_t lda, const float* B, int64_t ldb, float* C, int64_t ldc,
+                   const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                   float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                   float* workspace, int64_t workspace_floats,
+                   const float* elu_out, int64_t ld_eo, const float* B_lo, void* stream);
+
+/* lo[i] = rn_tf32(x[i] - trunc19(x[i])): the low plane of the 3xTF32 operand split (x ~ trunc19(x) + lo), n % 4 == 0,
+ * 16-byte aligned.  No counterpart in the reference. */
+int grappa_split_lo(int64_t n, const float* x, float* lo, void* stream);
+
 /* dZ = dY * keepmask/(1-p) * act'(.) where the activation output is recovered as (Y - res1 - res2)*(1-p).
  * Backward of the epilogue of grappa_gemm (autograd of the call sites above).  res1/res2 may be NULL.
  * colsum_out (N, may be NULL): also returns sum_m dZ[m,:] (the bias gradient) from the same pass; needs scratch of

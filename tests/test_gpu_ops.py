@@ -429,3 +429,26 @@ def test_linear_multi_wave_grids(M, N, K):
     assert float((wg.grad.double() - dw).abs().max()) / float(dw.abs().max()) < 3e-6
     # run-to-run determinism
     assert torch.equal(ops.linear(x, w, b), ops.linear(x, w, b))
+
+
+@pytest.mark.parametrize("M,N,K", [(300, 512, 256), (1280, 2048, 512), (2000, 130, 96)])
+def test_presplit_weight_operand_is_bit_identical(M, N, K, monkeypatch):
+    """grappa_gemm_ex with B_lo from grappa_split_lo (weights split once instead of in every CTA and k-block) feeds the
+    tensor core exactly the operands the in-kernel split produces: forward and dX are bit-identical."""
+    torch.manual_seed(M + N)
+    x = torch.randn(M, K, device=DEV)
+    w = (torch.randn(N, K, device=DEV) / math.sqrt(K)).requires_grad_(True)
+    b = torch.randn(N, device=DEV) * 0.1
+    gout = torch.randn(M, N, device=DEV)
+    lo = ops.split_lo(w.detach())
+    hi = (w.detach().view(torch.int32) & -8192).view(torch.float32)
+    rec = hi.double() + lo.double()
+    assert float((rec - w.detach().double()).abs().max()) <= float(w.detach().abs().max()) * 2.0 ** -21
+    outs = []
+    for use in (False, True):
+        monkeypatch.setattr(ops, "WEIGHT_LO", {id(w): lo} if use else {})
+        xg = x.clone().requires_grad_(True)
+        y = ops.linear(xg, w, b, act=ops.ACT_ELU)
+        y.backward(gout)
+        outs.append((y.detach().clone(), xg.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
