@@ -242,6 +242,12 @@ static int gemm_impl(int layout, int64_t M, int64_t N, int64_t K,
     p.b_vec = aligned16(B) && (ldb % 4 == 0);
     p.c_vec = aligned16(C) && (ldc % 4 == 0);
     cudaStream_t st = (cudaStream_t)stream;
+    {                                                           // one dimension <= 8: streaming kernels (gemm_skinny.cu)
+        bool handled = false;
+        int rc = gemm_skinny_dispatch(layout, p, st, workspace, workspace_floats, &handled);
+        if (rc) return rc;
+        if (handled) return 0;
+    }
     if (math_mode == 1) {
         bool handled = false;
         int rc = gemm_tc_dispatch(layout, p, st, workspace, workspace_floats, &handled);

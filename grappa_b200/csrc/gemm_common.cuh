@@ -23,6 +23,10 @@ __device__ __forceinline__ float elu_grad_from_out(float s) { return s > 0.f ? 1
 int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
                      bool* handled);   // gemm_tc.cu
 
+// streaming kernels for GEMMs with one dimension <= 8 (gemm_skinny.cu)
+int gemm_skinny_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
+                         bool* handled);
+
 // C = epilogue(sum_z partial[z]) in fixed order; shared by both GEMM paths (gemm_tc.cu)
 int splitk_reduce(const GemmParams& p, int splits, const float* partial, cudaStream_t st);
 

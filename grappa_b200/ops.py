@@ -4,6 +4,7 @@ current stream and the autograd tape; every arithmetic step is a kernel of libgr
 CPU tensors are rejected.
 """
 import ctypes
+import weakref
 from typing import Optional
 
 import numpy as np
@@ -197,6 +198,7 @@ def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, l
 # flat lo buffer next to its flat parameter buffer and refreshes it after every AdamW launch; without a driver (inference)
 # lo planes are made on first use and cached per weight version.
 WEIGHT_LO = None
+WEIGHT_EPOCH = [0]        # bumped by every optimiser launch of this library (its kernels do not touch tensor versions)
 USE_WEIGHT_LO = _os.environ.get("GRAPPA_WEIGHT_LO", "1") != "0"
 _LO_CACHE = {}
 
@@ -214,14 +216,14 @@ def weight_lo(w: torch.Tensor):
         return None
     if WEIGHT_LO is not None:
         return WEIGHT_LO.get(id(w))
-    if torch.is_grad_enabled() and w.requires_grad:
-        return None                       # plain autograd use: weights change behind our back
     key = id(w)
     hit = _LO_CACHE.get(key)
-    if hit is not None and hit[0] == w._version and hit[1] == w.data_ptr():
+    # ids and device addresses are recycled once a tensor dies: an entry is only valid for the very object it was made for
+    stamp = (w._version, w.data_ptr(), WEIGHT_EPOCH[0])
+    if hit is not None and hit[0]() is w and hit[1] == stamp:
         return hit[2]
     lo = split_lo(w.detach())
-    _LO_CACHE[key] = (w._version, w.data_ptr(), lo)
+    _LO_CACHE[key] = (weakref.ref(w, lambda _r, k=key: _LO_CACHE.pop(k, None)), stamp, lo)
     return lo
 
 

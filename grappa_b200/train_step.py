@@ -307,6 +307,7 @@ class TrainStep:
         _lib.check(_lib.lib().grappa_adamw(hi - lo, ptr(f.params), ptr(f.grads), ptr(f.exp_avg), ptr(f.exp_avg_sq),
                                            self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
                                            getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
+        ops.WEIGHT_EPOCH[0] += 1         # invalidates lo planes cached for use outside this driver
         if ops.USE_WEIGHT_LO:            # lo planes of the updated weights for the next step's GEMMs (B operand pre-split)
             _lib.check(_lib.lib().grappa_split_lo(hi - lo, ptr(f.params), ptr(f.params_lo), ops._stream()))
 

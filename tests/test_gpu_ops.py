@@ -452,3 +452,25 @@ def test_presplit_weight_operand_is_bit_identical(M, N, K, monkeypatch):
         y.backward(gout)
         outs.append((y.detach().clone(), xg.grad.clone()))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+@pytest.mark.parametrize("M,N_out", [(6080, 6), (4352, 2), (100, 1), (20000, 8), (63, 2)])
+def test_skinny_output_layer_forward_and_backward(M, N_out):
+    """Last symmetriser layer (256 -> 2 / 6): forward, dX (with the fused ELU') and dW run on the streaming kernels of
+    gemm_skinny.cu (one matrix dimension <= 8); against float64 PyTorch."""
+    torch.manual_seed(M + N_out)
+    x = torch.randn(M, 256, device=DEV)
+    w1, b1 = torch.randn(256, 256, device=DEV) / 16, torch.randn(256, device=DEV) * 0.1
+    w2, b2 = torch.randn(N_out, 256, device=DEV) / 16, torch.randn(N_out, device=DEV) * 0.1
+    gout = torch.randn(M, N_out, device=DEV)
+    leaves = [t.clone().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    y = ops.elu_mlp(*leaves)
+    y.backward(gout)
+    ref = [t.double().clone().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    yr = F.elu(ref[0] @ ref[1].T + ref[2]) @ ref[3].T + ref[4]
+    yr.backward(gout.double())
+    for a, b, name in zip([y] + [t.grad for t in leaves], [yr] + [t.grad for t in ref], ("y", "dx", "dw1", "db1", "dw2", "db2")):
+        scale = float(b.abs().max()) + 1e-30
+        assert float((a.double() - b).abs().max()) / scale < 5e-6, name
+    y2 = ops.elu_mlp(*[t.detach() for t in leaves])
+    assert torch.equal(y.detach(), y2)                      # deterministic
