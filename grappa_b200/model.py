@@ -59,6 +59,7 @@ _WRITER_STREAMS = {}
 # distinct (atom, pe) row instead of once per token whenever there are at least DEDUP_RATIO times more tokens than rows.
 DEDUP_TOKENS = True
 DEDUP_RATIO = 1.5
+FOLD_SYMMETRISER = True       # inference: the symmetriser's permutations folded into weight views (Symmetriser._forward_folded)
 WRITER_STREAM_PRIORITIES = (-1, -1, -2, -1)
 
 
@@ -346,8 +347,50 @@ class Symmetriser(nn.Module):
     def forward(self, x, T):
         """perm_equiv_transformer.py:257-294 up to (not including) the prefactor-weighted sum over permutations,
         which is fused with the range maps in the writers.  Returns (n_perm*T, out_feats)."""
+        if FOLD_SYMMETRISER and not torch.is_grad_enabled() and T > 0:
+            return self._forward_folded(x, T)
         rows = ops.symm_permute(x, T, self.n_seq, self._perms_host)
         for layer in self.mlp:
+            rows = layer(rows)
+        return rows
+
+    # ---- inference: permutations folded into the first layer's weights -------------------------------------------------
+    def _folded_weights(self):
+        """All permutations of a tuple share the LayerNorm statistics of the first layer (same multiset of values), so
+        LN(x_perm; gamma, beta) = gamma (.) P x_hat + beta with x_hat the normalised un-permuted tokens, and
+        W1 LN(x_perm) + b1 = (W1 diag(gamma) P) x_hat + (W1 beta + b1).  One weight view per permutation, cached per
+        weight version."""
+        ff = self.mlp[0]
+        ps = (ff.norm1.weight, ff.norm1.bias, ff.linear1.weight, ff.linear1.bias)
+        stamp = tuple((q._version, q.data_ptr()) for q in ps) + (ops.WEIGHT_EPOCH[0],)
+        c = getattr(self, "_fold", None)
+        if c is not None and c[0] == stamp:
+            return c[1]
+        g, b, w1, b1 = (q.detach() for q in ps)
+        H, D = w1.shape
+        E = D // self.n_seq
+        wv = (w1 * g[None, :]).view(H, self.n_seq, E)
+        views = []
+        for perm in self._perms_host:                   # x_perm block i = x block perm[i]  ->  column block j takes block i with perm[i] = j
+            inv = [perm.index(j) for j in range(self.n_seq)]
+            wp = wv[:, inv, :].reshape(H, D).contiguous()
+            views.append((wp, ops.split_lo(wp) if ops.USE_WEIGHT_LO and ops.MATH_MODE == 1 else None))
+        bias = torch.addmv(b1, w1, b).contiguous()
+        ones, zeros = torch.ones_like(g), torch.zeros_like(g)
+        out = (views, bias, ones, zeros)
+        self._fold = (stamp, out)
+        return out
+
+    def _forward_folded(self, x, T):
+        ff = self.mlp[0]
+        views, bias, ones, zeros = self._folded_weights()
+        H, D = ff.linear1.weight.shape
+        xh = ops.layer_norm(x.view(T, D), ones, zeros)                      # x_hat: statistics once per tuple
+        z = torch.empty((len(views) * T, H), device=x.device, dtype=torch.float32)
+        for p_i, (wp, lo) in enumerate(views):                              # rows [p T, (p+1) T) = permutation p
+            ops.gemm(0, T, H, D, xh, D, wp, D, z[p_i * T:(p_i + 1) * T], H, bias=bias, act=ops.ACT_ELU, b_lo=lo)
+        rows = ops.linear(z, ff.linear2.weight, ff.linear2.bias)
+        for layer in list(self.mlp)[1:]:
             rows = layer(rows)
         return rows
 

@@ -420,3 +420,32 @@ def test_shape_cache_is_bounded_and_evicted_shapes_still_train():
             assert torch.isfinite(loss)
             assert len(ts._static) <= 2
     assert shapes[0].signature not in ts._static and shapes[2].signature in ts._static
+
+
+def test_folded_symmetriser_matches_the_explicit_permutations(monkeypatch):
+    """Inference folds the symmetriser's permutations and the first LayerNorm's affine into weight views (shared
+    statistics per tuple): same parameters as the explicit permuted copies, for both model configurations, and the fold
+    follows weight updates."""
+    import grappa_b200.model as M
+    g_host = batch([S.trimer_molecule(seed=s, n_confs=2) for s in range(3)] +
+                   [S.make_molecule(S.template_ace_ala_nme(), seed=4, n_confs=2, with_reference_data=True)])
+    for make in (lambda: build_model()[0], lambda: GrappaModel().to(DEV).eval()):
+        model = make()
+        outs = []
+        for fold in (False, True, True):
+            monkeypatch.setattr(M, "FOLD_SYMMETRISER", fold)
+            if len(outs) == 2:                        # change the weights in place: the cached fold must be rebuilt
+                with torch.no_grad():
+                    for p in model.parameters():
+                        p.mul_(1.01)
+                monkeypatch.setattr(M, "FOLD_SYMMETRISER", False)
+                with torch.no_grad():
+                    ref2 = graph_params(model(g_host.to(DEV)))
+                monkeypatch.setattr(M, "FOLD_SYMMETRISER", True)
+            with torch.no_grad():
+                outs.append(graph_params(model(g_host.to(DEV))))
+        for lvl in LEVELS:
+            for key, v in outs[0][lvl].items():
+                scale = float(v.abs().max()) + 1e-12
+                assert float((v - outs[1][lvl][key]).abs().max()) / scale < 2e-5, f"{lvl} {key}"
+                assert float((ref2[lvl][key] - outs[2][lvl][key]).abs().max()) / (float(ref2[lvl][key].abs().max()) + 1e-12) < 2e-5
