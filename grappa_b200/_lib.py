@@ -43,8 +43,8 @@ PROTOTYPES = {
     "grappa_symm_permute_bwd": (I, [I64, I, I, I, P, P, P, P]),
     "grappa_readout_finalize_fwd": (I, [I, I64, I, I, P, P, P, P, P, I, I, P, P, P, P]),
     "grappa_readout_finalize_bwd": (I, [I, I64, I, I, P, P, P, P, P, I, I, P, P, P, P]),
-    "grappa_energy_plan_build": (I, [I64, I64, P, P, I64, P, I64, P, I64, P, I64, I, P, P, P, P, P, P, P, P]),
-    "grappa_energy_fwd": (I, [I64, I64, I64, P, I64, P, P, P, P, P, P, I, I, I, I, P, P, P, P, P, I, P, I,
+    "grappa_energy_plan_build": (I, [I64, I64, P, P, I64, P, I64, P, I64, P, I64, I, I, P, P, P, P, P]),
+    "grappa_energy_fwd": (I, [I64, I64, I64, P, I64, P, P, P, P, I, P, P, P, P, P, I, P, I,
                               P, P, P, P, P, P, P, P, P, P, P, P, P]),
     "grappa_energy_vjp": (I, [I64, P, P, P, P, P, I64, P, I64, P, I64, P, I64, P, P, P, P, P, I, P, I,
                               P, P, P, P, P, P, P]),

@@ -10,7 +10,7 @@ std::atomic<int64_t> g_launches{0};
 using namespace grappa;
 
 extern "C" const char* grappa_last_error(void) { return g_err; }
-extern "C" int grappa_abi_version(void) { return 1; }
+extern "C" int grappa_abi_version(void) { return 2; }
 extern "C" int64_t grappa_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 // Stable counting sort by key (host).  See include/grappa_b200.h.

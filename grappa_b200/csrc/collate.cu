@@ -16,8 +16,7 @@ constexpr int kSeg = 8;   // int64 per segment row
 // int segments: [src, dst, len, mode, a0, a1, a2, a3]
 //   mode 0: out[i] = store[src+i] + a0
 //   mode 1: energy block rows (12 ints): col 0 += a0 (atom), col 2 += a1 (molecule), col 3 += a2 (record)
-//   mode 2: record meta pairs (level|owner, tuple): tuple += a[level]
-//   mode 3: record atoms (4 per record): += a0 where position < n_seq(level); level from store[a1 + 2*record]
+//           (the energy kernel's per-block tuple programs are block- / molecule-relative: plain mode-0 copies)
 //   mode 4: out[i] = a0
 //   mode 5: out[i] = lit[src+i]                       (literals uploaded with the table: per-molecule offsets)
 __global__ void __launch_bounds__(256) collate_int_kernel(const int64_t* __restrict__ seg, const int32_t* __restrict__ store,
@@ -25,7 +24,7 @@ __global__ void __launch_bounds__(256) collate_int_kernel(const int64_t* __restr
     const int64_t* s = seg + (int64_t)blockIdx.x * kSeg;
     const int64_t src = s[0], dst = s[1], len = s[2];
     const int mode = (int)s[3];
-    const int32_t a0 = (int32_t)s[4], a1 = (int32_t)s[5], a2 = (int32_t)s[6], a3 = (int32_t)s[7];
+    const int32_t a0 = (int32_t)s[4], a1 = (int32_t)s[5], a2 = (int32_t)s[6];
     for (int64_t i = threadIdx.x; i < len; i += blockDim.x) {
         int32_t v;
         switch (mode) {
@@ -33,20 +32,6 @@ __global__ void __launch_bounds__(256) collate_int_kernel(const int64_t* __restr
             case 1: {
                 const int c = (int)(i % 12);
                 v = store[src + i] + (c == 0 ? a0 : c == 2 ? a1 : c == 3 ? a2 : 0);
-                break;
-            }
-            case 2: {
-                v = store[src + i];
-                if (i & 1) {
-                    const int lvl = store[src + i - 1] & 3;
-                    v += lvl == 0 ? a0 : lvl == 1 ? a1 : lvl == 2 ? a2 : a3;
-                }
-                break;
-            }
-            case 3: {
-                const int lvl = store[s[5] + 2 * (i >> 2)] & 3;
-                const int n_seq = lvl == 0 ? 2 : lvl == 1 ? 3 : 4;
-                v = store[src + i] + (((int)(i & 3) < n_seq) ? a0 : 0);
                 break;
             }
             case 4: v = a0; break;

@@ -85,7 +85,7 @@ GHD void dihedral_geom(V3 p0, V3 p1, V3 p2, V3 p3, float& cphi, float& sphi, V3 
     float iG = G2 > kTiny ? rsqrt_(G2) : 0.f;
     float Gn = G2 * iG;
     float x = dot(A, B);
-    float y = dot(cross(A, B), G) * iG;
+    float y = -dot(A, H) * Gn;      // (A x B).G / |G| with A x B = (F x G) x (H x G) = -(A.H) G
     float rho2 = x * x + y * y;
     float irho = rho2 > kTiny ? rsqrt_(rho2) : 0.f;
     cphi = rho2 > kTiny ? x * irho : 1.f;

@@ -678,8 +678,8 @@ class EnergyFn(torch.autograd.Function):
         ts = [torch.empty((T[l], C), device=dev, dtype=torch.float32) if want_coords else None for l in lv]
         partial = torch.empty((es["n_blocks"], 4, C), device=dev, dtype=torch.float32) if es["any_multi"] else None
         _lib.check(_lib.lib().grappa_energy_fwd(
-            N, n_mol, C, _p(xyz), es["n_blocks"], plan.ptr("e_blk"), plan.ptr("e_rec_atoms"), plan.ptr("e_rec_meta"),
-            plan.ptr("e_rec_slot"), plan.ptr("e_pull_ptr"), plan.ptr("e_pull_slot"), es["max_slots"], es["max_atoms"], es["any_multi"], term_mask,
+            N, n_mol, C, _p(xyz), es["n_blocks"], plan.ptr("e_blk"), plan.ptr("e_prog"), plan.ptr("e_mol_toff"),
+            plan.energy_sizes_array().ctypes.data, term_mask,
             _p(k2), _p(eq2), _p(k3), _p(eq3), _p(k4), P4, _p(k4i), P4i, _p(energy), _p(term), _p(grad),
             _p(xs[0]), _p(xs[1]), _p(xs[2]), _p(xs[3]), _p(ts[0]), _p(ts[1]), _p(ts[2]), _p(ts[3]), _p(partial), _stream()))
         ctx.save_for_backward(xyz, k2, eq2, k3, eq3, k4, k4i)

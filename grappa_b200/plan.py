@@ -8,7 +8,7 @@ buffer and moved to the device with a single copy:
   - atom -> token-row incidence CSR per level                (pull-style backward of the tuple gather)
   - (atom, pe) table row per token + its CSR for the levels with a positional-encoding column
                                                              (token de-duplication of the first LayerNorm + QKV)
-  - the energy kernel's atom-block / tuple-record / staging-slot tables  (grappa_energy_plan_build)
+  - the energy kernel's atom-block table and per-block tuple programs     (grappa_energy_plan_build)
   - per-molecule offsets of atoms / proper / improper rows   (segmenting, fused loss)
 
 The reference has no such object: it re-derives the same information on every call through advanced indexing and
@@ -16,6 +16,7 @@ DGL's segment bookkeeping (models/interaction_parameters.py:184, models/internal
 models/energy.py:69).  Index bounds are validated here (reference: models/grappa.py:179-185 does it with a device sync).
 """
 import ctypes
+import os
 from typing import Dict, Optional
 
 import numpy as np
@@ -25,6 +26,10 @@ from . import _lib
 from .graph import LEVELS, N_SEQ, get_bond_edges
 
 ENERGY_BLOCK_ATOMS = 64
+ENERGY_PARTS = 4          # warps per CTA of the energy kernel = parts of a block's tuple program
+# grappa_energy_plan_build's sizes_out[12]; under batching the first two add up, the others are maxima
+ENERGY_SIZE_KEYS = ("n_blocks", "n_words", "max_words", "max_slots", "max_atoms", "any_multi", "n_parts",
+                    "max_t2", "max_t3", "max_t4", "max_t4i", "any_nonlocal")
 # positional-encoding column of the default architecture per level (perm_equiv_transformer.py:189-199); bonds have none.
 # The (atom, pe) token tables below are built for these patterns; a model with another encoding does not use them.
 PE_PATTERN = {"n3": (0, 1, 0), "n4": (0, 1, 1, 0), "n4_improper": (0, 1, 1, 0)}
@@ -79,12 +84,20 @@ class BatchPlan:
         out.host = self.host.pin_memory()
         return out
 
+    def energy_sizes_array(self) -> np.ndarray:
+        """The plan's sizes in the order grappa_energy_fwd expects (host int64[12])."""
+        a = getattr(self, "_es_arr", None)
+        if a is None or self._es_src is not self.energy_sizes:
+            a = np.asarray([self.energy_sizes[k] for k in ENERGY_SIZE_KEYS], np.int64)
+            self._es_arr, self._es_src = a, self.energy_sizes
+        return a
+
     @property
     def h2d_bytes(self) -> int:
         return int(self.host.numel()) * 4
 
 
-def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS) -> BatchPlan:
+def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] = None) -> BatchPlan:
     L = _lib.lib()
     p = BatchPlan()
     n_atoms = int(g.num_nodes("n1"))
@@ -147,31 +160,27 @@ def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS) -> BatchPlan:
         arrays[name + "_nbr"] = other[order].astype(np.int32)
 
     # energy plan
-    sizes = np.zeros(8, np.int64)
+    sizes = np.zeros(12, np.int64)
     args_idx = []
+    keep = []
     for lvl in LEVELS:
         a = np.ascontiguousarray(idx64[lvl].reshape(-1))
         args_idx += [_np_ptr(a), p.T[lvl]]
-        arrays["_keep_" + lvl] = a   # keep alive until the second call
-    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, _np_ptr(sizes),
-                                          None, None, None, None, None, None, None))
-    nB, nR, nP = int(sizes[0]), int(sizes[1]), int(sizes[2])
+        keep.append(a)   # keep alive until the second call
+    if n_parts is None:
+        n_parts = int(os.environ.get("GRAPPA_ENERGY_PARTS", ENERGY_PARTS))
+    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, n_parts,
+                                          _np_ptr(sizes), None, None, None, None))
+    nB, nW = int(sizes[0]), int(sizes[1])
     blk = np.zeros(nB * 12, np.int32)
-    rec_atoms = np.zeros(nR * 4, np.int32)
-    rec_meta = np.zeros(nR * 2, np.int32)
-    rec_slot = np.zeros(nR * 4, np.int32)
-    pull_ptr = np.zeros(n_atoms + 1, np.int32)
-    pull_slot = np.zeros(nP, np.int32)
+    prog = np.zeros(nW, np.int32)
+    mol_toff = np.zeros(4 * (p.n_mol + 1), np.int32)
     tuple_mol = np.zeros(sum(p.T.values()), np.int32)
-    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, _np_ptr(sizes),
-                                          _np_ptr(blk), _np_ptr(rec_atoms), _np_ptr(rec_meta), _np_ptr(rec_slot),
-                                          _np_ptr(pull_ptr), _np_ptr(pull_slot), _np_ptr(tuple_mol)))
-    p.energy_sizes = dict(n_blocks=nB, n_records=nR, n_pull=nP, max_slots=int(sizes[3]), max_records=int(sizes[4]),
-                          max_atoms=int(sizes[5]), any_multi=int(sizes[6]))
-    for lvl in LEVELS:
-        del arrays["_keep_" + lvl]
-    arrays.update(e_blk=blk, e_rec_atoms=rec_atoms, e_rec_meta=rec_meta, e_rec_slot=rec_slot, e_pull_ptr=pull_ptr,
-                  e_pull_slot=pull_slot, tuple_mol=tuple_mol)
+    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, n_parts,
+                                          _np_ptr(sizes), _np_ptr(blk), _np_ptr(prog), _np_ptr(mol_toff), _np_ptr(tuple_mol)))
+    del keep
+    p.energy_sizes = dict(zip(ENERGY_SIZE_KEYS, (int(v) for v in sizes)))
+    arrays.update(e_blk=blk, e_prog=prog, e_mol_toff=mol_toff, tuple_mol=tuple_mol)
 
     # per-molecule offsets (int32) for the fused loss / segmenting
     arrays["mol_atom_off"] = mol_atom_off.astype(np.int32)

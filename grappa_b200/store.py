@@ -24,9 +24,10 @@ import torch
 from . import _lib
 from .batching import DeviceBatch, _FLOAT_FIELDS
 from .graph import LEVELS, N_SEQ, HeteroGraph, conf_indices, delete_dummy_confs
-from .plan import BatchPlan, build_plan
+from .plan import ENERGY_SIZE_KEYS, BatchPlan, build_plan
 
-_SIZE_KEYS = ("n_blocks", "n_records", "n_pull", "max_slots", "max_records", "max_atoms", "any_multi")
+_SIZE_KEYS = ENERGY_SIZE_KEYS
+_SUM_KEYS = ("n_blocks", "n_words")
 
 
 def _pad4(n: int) -> int:
@@ -169,7 +170,7 @@ class MoleculeStore:
         cum = lambda a: np.concatenate([[0], np.cumsum(a)]).astype(np.int64)
         Ac, Ec = cum(N), cum(E)
         Tc = {lvl: cum(T[lvl]) for lvl in LEVELS}
-        Bc, Rc, Pc = cum(sz["n_blocks"]), cum(sz["n_records"]), cum(sz["n_pull"])
+        Bc, Wc = cum(sz["n_blocks"]), cum(sz["n_words"])
         nA, nE = int(Ac[-1]), int(Ec[-1])
         has_xyz = ("n1", "xyz") in self.f_off
         C = self.n_confs_for(ids, conf_strategy) if has_xyz else 0
@@ -188,9 +189,9 @@ class MoleculeStore:
         plan.T = {lvl: int(Tc[lvl][-1]) for lvl in LEVELS}
         plan.levels_present = self.levels_present
         plan.mol_atom_counts = N.copy()
-        plan.energy_sizes = dict(n_blocks=int(Bc[-1]), n_records=int(Rc[-1]), n_pull=int(Pc[-1]),
-                                 max_slots=int(sz["max_slots"].max()), max_records=int(sz["max_records"].max()),
-                                 max_atoms=int(sz["max_atoms"].max()), any_multi=int(sz["any_multi"].max()))
+        plan.energy_sizes = {k: int(sz[k].sum()) if k in _SUM_KEYS else int(sz[k].max()) for k in _SIZE_KEYS}
+        if int(sz["n_parts"].min()) != plan.energy_sizes["n_parts"]:
+            raise ValueError("all molecules of a store must be planned with the same number of energy parts")
         T_all = sum(plan.T.values())
         lengths = {}
         for lvl in LEVELS:
@@ -202,8 +203,7 @@ class MoleculeStore:
             lengths["tab_ptr_" + lvl] = 2 * nA + 1
             lengths["tab_tok_" + lvl] = N_SEQ[lvl] * plan.T[lvl]
         lengths.update(in_ptr=nA + 1, out_ptr=nA + 1, in_nbr=nE, out_nbr=nE, e_blk=12 * int(Bc[-1]),
-                       e_rec_atoms=4 * int(Rc[-1]), e_rec_meta=2 * int(Rc[-1]), e_rec_slot=4 * int(Rc[-1]),
-                       e_pull_ptr=nA + 1, e_pull_slot=int(Pc[-1]), tuple_mol=T_all, mol_atom_off=B + 1)
+                       e_prog=int(Wc[-1]), e_mol_toff=4 * (B + 1), tuple_mol=T_all, mol_atom_off=B + 1)
         total = 0
         for name in self.int_names:
             plan.offsets[name] = (total, int(lengths[name]))
@@ -256,17 +256,11 @@ class MoleculeStore:
             elif name in ("in_nbr", "out_nbr"):
                 seg(name, Ec[:-1], ln, 0, Ac[:-1])
             elif name == "e_blk":
-                seg(name, 12 * Bc[:-1], ln, 1, Ac[:-1], mol, Rc[:-1])
-            elif name == "e_rec_atoms":
-                seg(name, 4 * Rc[:-1], ln, 3, Ac[:-1], self.i_off["e_rec_meta"][ids])
-            elif name == "e_rec_meta":
-                seg(name, 2 * Rc[:-1], ln, 2, *[Tc[lvl][:-1] for lvl in LEVELS])
-            elif name == "e_rec_slot":
-                seg(name, 4 * Rc[:-1], ln, 0)
-            elif name == "e_pull_ptr":
-                seg(name, Ac[:-1], ln, 0, Pc[:-1])
-            elif name == "e_pull_slot":
-                seg(name, Pc[:-1], ln, 0)
+                seg(name, 12 * Bc[:-1], ln, 1, Ac[:-1], mol, Wc[:-1])
+            elif name == "e_prog":
+                seg(name, Wc[:-1], ln, 0)          # every program word is relative to its block / molecule
+            elif name == "e_mol_toff":
+                literal(name, np.concatenate([Tc[lvl] for lvl in LEVELS]))
             elif name == "tuple_mol":
                 for lvl in LEVELS:
                     seg(name, tuple_base + Tc[lvl][:-1], T[lvl], 4, mol, src=zeros)

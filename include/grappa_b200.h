@@ -201,32 +201,37 @@ int grappa_readout_finalize_bwd(int kind, int64_t T, int P, int n_out, const flo
  * MM energy + analytic dE/dxyz.  Replaces internal_coordinates (internal_coordinates.py:19-115),
  * harmonic_energy / torsion_energy / pool_energy (energy.py:8-71) and the autograd.grad call (energy.py:160-164).
  *
- * The host plan partitions the atoms of every molecule into blocks of <= block_atoms consecutive atoms and lists,
- * per block, every tuple touching it (tuples spanning blocks are evaluated once per block they touch; only the
- * owner block adds their energy).  grappa_energy_plan_build fills caller-provided HOST int32 arrays; call it first
- * with all output pointers NULL to obtain the sizes in sizes_out[8] =
- *   {n_blocks, n_records, n_pull, max_slots_per_block, max_records_per_block, max_atoms_per_block, any_multi_block, 0}.
- * idx2/3/4/4i: HOST int64 (T,n_seq) global atom rows; mol_atom_off: HOST int64 (n_mol+1).
+ * The host plan partitions the atoms of every molecule into blocks of <= block_atoms consecutive atoms and compiles,
+ * per block, a PROGRAM of every tuple touching it, split into n_parts balanced parts (one per warp of the kernel's
+ * CTA); tuples spanning blocks are evaluated once per block they touch, only the owner block adds their energy.
+ * Record / word formats: csrc/energy.cu.  All program words are relative to the block or its molecule, so per-molecule
+ * plans concatenate into a batch plan by offsetting columns 0 / 2 / 3 of the block rows (grappa_collate_int mode 1).
+ * grappa_energy_plan_build fills caller-provided HOST int32 arrays; call it first with blk == NULL to obtain
+ *   sizes_out[12] = {n_blocks, n_words, max_words_per_block, max_slots_per_part, max_atoms_per_block, any_multi_block,
+ *                    n_parts, max tuples of one molecule at level n2, n3, n4, n4_improper, any_non_local_block}.
+ * idx2/3/4/4i: HOST int64 (T,n_seq) global atom rows, rows grouped by molecule in molecule order (as dgl.batch
+ * produces); mol_atom_off: HOST int64 (n_mol+1).  mol_tuple_off: (4, n_mol+1) first tuple row of every molecule per
+ * level; tuple_mol (may be NULL): molecule of every tuple, levels concatenated.
  */
 int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
                              const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
                              const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
-                             int block_atoms, int64_t* sizes_out,
-                             int32_t* blk /*(n_blocks,12)*/, int32_t* rec_atoms /*(n_records,4)*/,
-                             int32_t* rec_meta /*(n_records,2)*/, int32_t* rec_slot /*(n_records,4)*/,
-                             int32_t* pull_ptr /*(n_atoms+1)*/, int32_t* pull_slot /*(n_pull)*/,
-                             int32_t* tuple_mol /*(T2+T3+T4+T4i)*/);
+                             int block_atoms, int n_parts, int64_t* sizes_out,
+                             int32_t* blk /*(n_blocks,12)*/, int32_t* prog /*(n_words)*/,
+                             int32_t* mol_tuple_off /*(4,n_mol+1)*/, int32_t* tuple_mol /*(T2+T3+T4+T4i)*/);
 
-/* All plan arrays are the device copies of the arrays above.  k4: (T4,P4), k4i: (T4i,P4i).
+/* blk / prog / mol_tuple_off are the device copies of the arrays above; plan_sizes is the HOST sizes_out[12] of the
+ * plan (for a concatenated batch plan: sums of n_blocks / n_words, maxima of the rest).  k4: (T4,P4), k4i: (T4i,P4i).
  * Outputs: energy (n_mol,C) total; term_energy (4,n_mol,C); gradient (N,C,3) = +dE/dxyz.
  * Optional (may be NULL): x2,x3,x4,x4i (T,C) internal coordinates; e2,e3,e4,e4i (T,C) per-tuple energies.
  * partial: scratch (n_blocks,4,C) floats, used only when a molecule spans several blocks.
  * term_mask: bit l set = include level l (0 bond, 1 angle, 2 proper, 3 improper); 15 = all.  Sub-masks give the
- * per-term gradients of Energy(gradient_contributions=True) (energy.py:146-152). */
+ * per-term gradients of Energy(gradient_contributions=True) (energy.py:146-152).
+ * Coordinate and gradient rows move through the TMA engine (cp.async.bulk) when C % 4 == 0 and xyz / gradient are
+ * 16-byte aligned, through coalesced loads / stores otherwise; results are identical. */
 int grappa_energy_fwd(int64_t n_atoms, int64_t n_mol, int64_t C, const float* xyz,
-                      int64_t n_blocks, const int32_t* blk, const int32_t* rec_atoms, const int32_t* rec_meta,
-                      const int32_t* rec_slot, const int32_t* pull_ptr, const int32_t* pull_slot,
-                      int max_slots, int max_block_atoms, int any_multi_block, int term_mask,
+                      int64_t n_blocks, const int32_t* blk, const int32_t* prog, const int32_t* mol_tuple_off,
+                      const int64_t* plan_sizes /*HOST (12)*/, int term_mask,
                       const float* k2, const float* eq2, const float* k3, const float* eq3,
                       const float* k4, int P4, const float* k4i, int P4i,
                       float* energy, float* term_energy, float* gradient,
@@ -265,8 +270,7 @@ int grappa_enumerate_tuples(int64_t n_bonds, const int64_t* bonds, int64_t n_ato
  * utils/dgl_utils.py:11-63 (idxs offsetting + concatenation) by two gather launches over a packed per-molecule store
  * that is resident in HBM.  seg: device (n_seg,8) int64 segment rows, one CTA each:
  *   int rows   [src, dst, len, mode, a0, a1, a2, a3]   mode 0 copy+a0 | 1 energy-block rows (col0+a0, col2+a1, col3+a2)
- *              | 2 record meta (tuple += a[level]) | 3 record atoms (+a0 where pos < n_seq; a1 = store offset of the
- *              molecule's record meta) | 4 fill a0 | 5 copy from lit[src..]
+ *              | 4 fill a0 | 5 copy from lit[src..]   (modes 2, 3 retired with the record tables of ABI version 1)
  *   float rows [src, dst, rows, inner, C_src, C_dst, conf_off, mode]   mode 0 gather conformations conf[conf_off+c]
  *              (conf_off < 0: identity) | 1 is_dummy flags (c >= C_src).
  * store / out: device buffers (src / dst are element offsets into them); lit, conf: device int32. */

@@ -59,7 +59,7 @@ def test_prototypes_match_header():
 
 def test_loader_and_error_string():
     L = _lib.lib()
-    assert L.grappa_abi_version() == 1
+    assert L.grappa_abi_version() == 2
     # argument validation happens on the host before any launch: usable without a GPU
     rc = L.grappa_gemm(7, 1, 1, 1, None, 1, None, 1, None, 1, None, 0, None, 0, None, 0, 0.0, 0, None, 0, None, 0, None)
     assert rc != 0

@@ -21,14 +21,6 @@ def apply_int_segments(seg, store, lit, out):
         elif mode == 1:
             c = i % 12
             v = store[src:src + ln] + np.where(c == 0, a0, np.where(c == 2, a1, np.where(c == 3, a2, 0)))
-        elif mode == 2:
-            v = store[src:src + ln].copy()
-            lvl = v[0::2] & 3
-            v[1::2] += np.asarray([a0, a1, a2, a3])[lvl]
-        elif mode == 3:
-            lvl = store[a1 + 2 * (i >> 2)] & 3
-            n_seq = np.asarray([2, 3, 4, 4])[lvl]
-            v = store[src:src + ln] + np.where((i & 3) < n_seq, a0, 0)
         elif mode == 4:
             v = np.full(ln, a0)
         else:

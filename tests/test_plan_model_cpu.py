@@ -66,60 +66,109 @@ def test_plan_csr_and_incidence():
     np.testing.assert_array_equal(p.host_view("mol_off_n4"), np.concatenate([[0], np.cumsum(g.batch_num_nodes("n4").numpy())]))
 
 
-@pytest.mark.parametrize("block_atoms", [64, 16, 7])
-def test_energy_plan_invariants(block_atoms):
-    g = batch([S.trimer_molecule(s, 2) for s in (0, 1, 2)])
-    p = build_plan(g, block_atoms=block_atoms)
+def decode_energy_program(p, g):
+    """Interprets the energy plan (csrc/energy.cu: block rows + per-block programs) back into tuples per block."""
     es = p.energy_sizes
+    W = es["n_parts"]
     blk = p.host_view("e_blk").reshape(-1, 12)
-    rec_atoms = p.host_view("e_rec_atoms").reshape(-1, 4)
-    rec_meta = p.host_view("e_rec_meta").reshape(-1, 2)
-    rec_slot = p.host_view("e_rec_slot").reshape(-1, 4)
-    pull_ptr, pull_slot = p.host_view("e_pull_ptr"), p.host_view("e_pull_slot")
+    prog = p.host_view("e_prog")
+    toff = p.host_view("e_mol_toff").reshape(4, -1)
+    out = []
+    for b in range(len(blk)):
+        a0, na, mol, p0, nw, n_slots, nb, j, local = blk[b, :9]
+        assert p0 % 4 == 0 and nw % 4 == 0
+        pg = prog[p0:p0 + nw]
+        offs = pg[:W + 1]
+        smap = pg[W + 1:W + 1 + W * na].reshape(W, na)
+        assert offs[0] == W + 1 + W * na and offs[-1] <= nw
+        recs = []       # (part, level, tuple row, owner, atom rows)
+        for w in range(W):
+            pos = offs[w]
+            counts = pg[pos:pos + 4]
+            pos += 4
+            used = smap[w][smap[w] >= 0]
+            assert (used % 96 == 0).all() and len(set(used.tolist())) == len(used) and (used // 96 < n_slots).all()
+            touched = set()
+            for level, n, ns in ((2, counts[0], 4), (3, counts[1], 4), (1, counts[2], 3), (0, counts[3], 2)):
+                for _ in range(n):
+                    hdr = int(pg[pos])
+                    words = pg[pos + 1:pos + 1 + ns].astype(np.int64)
+                    if local:
+                        al, slot = (words & 0xffff), (words >> 16) & 0xffff
+                        assert (al % 384 == 0).all() and (slot % 384 == 0).all()
+                        al, slot = al // 384, slot // 384
+                        assert (smap[w][al] == slot * 96).all()      # the reduction map names the same slots
+                        atoms = a0 + al
+                    else:
+                        al = words
+                        atoms = a0 + words
+                        assert (smap[w] == 96 * np.arange(na)).all()
+                    touched.update(int(x) for x in al if 0 <= x < na)
+                    recs.append((w, level, int(toff[level, mol]) + (hdr >> 1), hdr & 1, atoms.tolist()))
+                    pos += 1 + ns
+            if local:
+                assert touched == set(np.nonzero(smap[w] >= 0)[0].tolist())
+            assert pos == offs[w + 1]
+        out.append(recs)
+    return blk, out
+
+
+@pytest.mark.parametrize("block_atoms,n_parts", [(64, 4), (16, 3), (7, 1), (64, 8), (64, 16)])
+def test_energy_plan_invariants(block_atoms, n_parts):
+    g = batch([S.trimer_molecule(s, 2) for s in (0, 1, 2)])
+    p = build_plan(g, block_atoms=block_atoms, n_parts=n_parts)
+    es = p.energy_sizes
+    blk, recs = decode_energy_program(p, g)
     n = g.num_nodes("n1")
     # blocks partition the atoms, never cross molecules, and respect the size limit
     assert blk[:, 1].sum() == n and (blk[:, 1] <= block_atoms).all()
     atom_blk = np.repeat(np.arange(len(blk)), blk[:, 1])
     mol_of_atom = np.repeat(np.arange(3), 40)
     assert (mol_of_atom == blk[atom_blk, 2]).all()
-    assert es["any_multi"] == int(block_atoms < 40)
-    n_seq = {0: 2, 1: 3, 2: 4, 3: 4}
+    assert es["any_multi"] == es["any_nonlocal"] == int(block_atoms < 40)
+    assert es["n_parts"] == n_parts and es["n_blocks"] == len(blk) and es["n_words"] == len(p.host_view("e_prog"))
+    assert es["max_words"] == blk[:, 4].max() and es["max_atoms"] == blk[:, 1].max()
     levels = ("n2", "n3", "n4", "n4_improper")
+    assert [es["max_t2"], es["max_t3"], es["max_t4"], es["max_t4i"]] == [int(g.batch_num_nodes(l).max()) for l in levels]
     owners = {l: np.zeros(g.num_nodes(l), int) for l in levels}
-    total_inc = 0
+    seen = {l: [set() for _ in range(len(blk))] for l in levels}
     for b in range(len(blk)):
-        r0, nr = blk[b, 3], blk[b, 4]
-        seen_slots = []
-        prev = (-1, -1)
-        for r in range(r0, r0 + nr):
-            level, owner, t = rec_meta[r, 0] & 3, (rec_meta[r, 0] >> 2) & 1, rec_meta[r, 1]
-            assert (level, t) > prev        # ordered by (level, tuple) inside a block
-            prev = (level, t)
+        per_kind = {}
+        for w, level, t, owner, atoms in recs[b]:
             idx = g.nodes[levels[level]].data["idxs"].numpy()[t]
-            np.testing.assert_array_equal(rec_atoms[r, :n_seq[level]], idx)
+            assert atoms == idx.tolist()                       # the record names the tuple's atoms, in order
+            assert (atom_blk[idx] == b).any()                  # and the tuple touches this block
+            assert blk[b, 8] == 0 or (atom_blk[idx] == b).all()
+            assert t not in seen[levels[level]][b]
+            seen[levels[level]][b].add(t)
             if owner:
                 owners[levels[level]][t] += 1
                 assert atom_blk[idx[0]] == b
-            for i in range(4):
-                inside = i < n_seq[level] and atom_blk[idx[i]] == b
-                assert (rec_slot[r, i] >= 0) == inside
-                if inside:
-                    seen_slots.append(rec_slot[r, i])
-                    a = idx[i]
-                    assert rec_slot[r, i] in pull_slot[pull_ptr[a]:pull_ptr[a + 1]]
-        assert sorted(seen_slots) == list(range(blk[b, 5]))     # slots are dense per block
-        lv = rec_meta[r0:r0 + nr, 0] & 3
-        assert [int((lv == l).sum()) for l in range(4)] == blk[b, 8:12].tolist()
-        total_inc += len(seen_slots)
-    for l in levels:
+            per_kind[w] = per_kind.get(w, 0) + {0: 3, 1: 8, 2: 10, 3: 10}[level]
+        c = [per_kind.get(w, 0) for w in range(n_parts)]        # parts are balanced by estimated cost
+        assert max(c) - min(c) <= 20
+    for li, l in enumerate(levels):
         assert (owners[l] == 1).all()       # every tuple's energy is counted exactly once
-    assert total_inc == es["n_pull"] == pull_ptr[-1] == sum(g.num_nodes(l) * s for l, s in zip(levels, (2, 3, 4, 4)))
+        idx = g.nodes[l].data["idxs"].numpy()
+        for t in range(len(idx)):           # and it is evaluated in exactly the blocks it touches
+            assert {b for b in range(len(blk)) if t in seen[l][b]} == set(atom_blk[idx[t]].tolist())
     tm = p.host_view("tuple_mol")
     off = 0
     for l in levels:
         idx = g.nodes[l].data["idxs"].numpy()
         np.testing.assert_array_equal(tm[off:off + len(idx)], mol_of_atom[idx[:, 0]])
         off += len(idx)
+    toff = p.host_view("e_mol_toff").reshape(4, -1)
+    for li, l in enumerate(levels):
+        np.testing.assert_array_equal(toff[li], np.concatenate([[0], np.cumsum(g.batch_num_nodes(l).numpy())]))
+
+
+def test_energy_plan_rejects_ungrouped_tuples():
+    g = batch([S.trimer_molecule(s, 2) for s in (0, 1)])
+    ix = g.nodes["n2"].data["idxs"].clone()
+    g.nodes["n2"].data["idxs"] = torch.flip(ix, dims=[0])      # molecule 1's bonds first
+    with pytest.raises(RuntimeError, match="grouped by molecule"):
+        build_plan(g)
 
 
 def test_plan_rejects_out_of_range_idxs():
@@ -136,4 +185,6 @@ def test_plan_handles_missing_and_empty_levels():
     g._num_nodes["n4_improper"] = 0
     g._batch_num_nodes["n4_improper"] = torch.tensor([0])
     p = build_plan(g)
-    assert p.T["n4_improper"] == 0 and p.energy_sizes["n_records"] == 21 + 36 + 41
+    assert p.T["n4_improper"] == 0 and p.energy_sizes["max_t4i"] == 0
+    _, recs = decode_energy_program(p, g)
+    assert len(recs) == 1 and len(recs[0]) == 21 + 36 + 41
