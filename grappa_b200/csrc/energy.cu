@@ -31,7 +31,9 @@ namespace grappa {
 //                       word of the program is relative to the block or to the molecule, so per-molecule plans
 //                       concatenate into a batch plan by adding three offsets per block row (csrc/collate.cu, mode 1).
 // Program of a block:   [off_0 .. off_W]  word offsets (relative to prog0) of the W parts,
-//                       [map[w][al]]      W x n_atoms: float offset (96 * slot) of atom al in part w's accumulator, or -1,
+//                       [pull_ptr[al]]    n_atoms + 1 offsets into the pull list (relative to its start),
+//                       [pull[..]]        per atom, in part order: part << 16 | 96 * slot  = the accumulator rows whose
+//                                         sum is the atom's gradient (phase 2 of the kernel),
 //                       then per part [n_proper, n_improper, n_angle, n_bond] followed by its records in that order:
 //                         torsion  [hdr, w0, w1, w2, w3]     hdr = t_local << 1 | owner
 //                         angle    [hdr, w0, w1, w2]
@@ -76,7 +78,7 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
     GRAPPA_CHECK_ARG(mol_atom_off[0] == 0 && mol_atom_off[n_mol] == n_atoms, "mol_atom_off must span [0, n_atoms]");
     LevelIdx lv[4] = {{idx2, T2, 2}, {idx3, T3, 3}, {idx4, T4, 4}, {idx4i, T4i, 4}};
     const int W = n_parts;
-    const int kCost[4] = {3, 8, 10, 10};              // relative cost of a bond / angle / torsion record
+    const int kCost[4] = {6, 14, 18, 18};              // relative cost of a bond / angle / torsion record (measured SASS instructions / 10)
     const int kOrder[4] = {3, 2, 0, 1};               // position of a level inside a part: propers, impropers, angles, bonds
     const int kWords[4] = {3, 4, 5, 5};
 
@@ -144,11 +146,11 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
     std::vector<int64_t> word0((size_t)nB + 1, 0);
     std::vector<uint8_t> local((size_t)nB, 1);
     std::vector<std::vector<int32_t>> part_of((size_t)nB);     // part of every item (after sorting)
-    std::vector<int32_t> n_slots((size_t)nB, 0);
+    std::vector<int32_t> n_slots((size_t)nB, 0), n_pull((size_t)nB, 0);
     for (int64_t b = 0; b < nB; ++b) {
         std::vector<PlanItem>& v = items[(size_t)b];
         std::stable_sort(v.begin(), v.end(), [](const PlanItem& x, const PlanItem& y) { return x.key < y.key; });
-        int64_t total = 0, w = (W + 1) + (int64_t)W * blocks[b].na + 4 * W;
+        int64_t total = 0, w = (W + 1) + (blocks[b].na + 1) + 4 * W;
         for (const PlanItem& it : v) {
             total += kCost[it.level];
             w += kWords[it.level];
@@ -164,7 +166,7 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
             run += c;
         }
         if (local[b]) {
-            int32_t ns = 0;
+            int32_t ns = 0, np_ = 0;
             std::vector<uint8_t> touched((size_t)W * std::max(1, (int)blocks[b].na), 0);
             std::vector<int32_t> cnt((size_t)W, 0);
             for (size_t i = 0; i < v.size(); ++i) {
@@ -174,11 +176,14 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
                     if (!f) { f = 1; cnt[po[i]]++; }
                 }
             }
-            for (int p = 0; p < W; ++p) ns = std::max(ns, cnt[p]);
+            for (int p = 0; p < W; ++p) { ns = std::max(ns, cnt[p]); np_ += cnt[p]; }
             n_slots[b] = std::max(ns, 1);
+            n_pull[b] = np_;
         } else {
             n_slots[b] = std::max(1, (int)blocks[b].na);
+            n_pull[b] = W * blocks[b].na;
         }
+        w += n_pull[b];
         w = (w + 3) / 4 * 4;
         word0[b + 1] = word0[b] + w;
         max_words = std::max(max_words, w);
@@ -206,9 +211,11 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
         o[0] = B.a0; o[1] = B.na; o[2] = B.mol; o[3] = (int32_t)word0[b]; o[4] = (int32_t)(word0[b + 1] - word0[b]);
         o[5] = n_slots[b]; o[6] = B.nb; o[7] = B.j; o[8] = local[b]; o[9] = o[10] = o[11] = 0;
         int32_t* pg = prog + word0[b];
-        int32_t* map = pg + (W + 1);
-        for (int64_t i = 0; i < (int64_t)W * B.na; ++i) map[i] = local[b] ? -1 : (int32_t)((i % B.na) * kRow);
-        int64_t pos = (W + 1) + (int64_t)W * B.na;
+        int32_t* pull_ptr = pg + (W + 1);
+        int32_t* pull = pull_ptr + (B.na + 1);
+        std::vector<int32_t> map((size_t)W * std::max(1, (int)B.na), -1);   // [w][al] -> 96 * slot
+        if (!local[b]) for (int64_t i = 0; i < (int64_t)W * B.na; ++i) map[i] = (int32_t)((i % B.na) * kRow);
+        int64_t pos = (W + 1) + (B.na + 1) + n_pull[b];
         size_t i0 = 0;
         for (int w = 0; w < W; ++w) {
             size_t i1 = i0;
@@ -231,7 +238,7 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
                     for (int q = 0; q < ns; ++q) {
                         const int64_t al = a[q] - B.a0;
                         if (local[b]) {
-                            int32_t& m = map[(int64_t)w * B.na + al];
+                            int32_t& m = map[(size_t)w * B.na + al];
                             if (m < 0) m = (next_slot++) * kRow;
                             pg[pos++] = (int32_t)((al * kRow * 4) | ((int64_t)m * 4 << 16));
                         } else {
@@ -242,6 +249,13 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
             }
             i0 = i1;
         }
+        int32_t np_ = 0;
+        for (int64_t al = 0; al < B.na; ++al) {
+            pull_ptr[al] = np_;
+            for (int w = 0; w < W; ++w)
+                if (map[(size_t)w * B.na + al] >= 0) pull[np_++] = (w << 16) | map[(size_t)w * B.na + al];
+        }
+        pull_ptr[B.na] = np_;
         pg[W] = (int32_t)pos;
         while (pos < word0[b + 1] - word0[b]) pg[pos++] = 0;
     }
@@ -326,9 +340,9 @@ __device__ __forceinline__ void torsion_terms(const float* __restrict__ k, float
 
 // Everything a record evaluation needs besides the record itself.
 struct LaneCtx {
-    const char* xl;        // shared coordinates + 12 * lane bytes
-    char* accw;            // this warp's accumulator + 12 * lane bytes
-    const float* halo;     // xyz + ((a0 * C + c0 + lane) * 3: positions of atoms outside the block
+    const char* __restrict__ xl;        // shared coordinates + 12 * lane bytes
+    char* __restrict__ accw;            // this warp's accumulator + 12 * lane bytes (never aliases xl / the program)
+    const float* __restrict__ halo;     // xyz + ((a0 * C + c0 + lane) * 3: positions of atoms outside the block
     int64_t C3, C, col;
     int na;
     bool blk_local;
@@ -378,7 +392,7 @@ __device__ __forceinline__ float torsion_loop(int n, const int* __restrict__ pw,
         acc3<LOCAL>(r1, dE, gg[1]);
         acc3<LOCAL>(r2, dE, gg[2]);
         acc3<LOCAL>(r3, dE, gg[3]);
-        if (hdr & 1) {
+        if (LOCAL || (hdr & 1)) {
             esum += E;
             if (MAT) {
                 const int64_t row = (int64_t)(toff + tl) * c.C + c.col;
@@ -507,7 +521,7 @@ __global__ void __launch_bounds__(kMaxEnergyThreads) energy_fwd_kernel(const Ene
                 acc3<LOCAL>(r0, f, g0);
                 acc3<LOCAL>(r1, -f, g0 + g2);
                 acc3<LOCAL>(r2, f, g2);
-                if (hdr & 1) {
+                if (LOCAL || (hdr & 1)) {
                     const float E = 0.5f * f * d;
                     e1 += E;
                     if (MAT) {
@@ -532,7 +546,7 @@ __global__ void __launch_bounds__(kMaxEnergyThreads) energy_fwd_kernel(const Ene
                 const float d = r_ - peq2[tl], f = pk2[tl] * d;
                 acc3<LOCAL>(r0, f, g0);
                 acc3<LOCAL>(r1, -f, g0);
-                if (hdr & 1) {
+                if (LOCAL || (hdr & 1)) {
                     const float E = 0.5f * f * d;
                     e0 += E;
                     if (MAT) {
@@ -552,18 +566,17 @@ __global__ void __launch_bounds__(kMaxEnergyThreads) energy_fwd_kernel(const Ene
 
     // ---- phase 2: every atom's row = sum over the parts that touch it, in part order; the rows leave through the
     //      coordinate buffer (TMA store) or directly (coalesced stores) ------------------------------------------------
-    const int* map = prog + (W + 1);                   // [W][na] float offset of the atom's slot, or -1
+    const int* pull_ptr = prog + (W + 1);
+    const int* pull = pull_ptr + (na + 1);             // part << 16 | float offset of the atom's slot in that part
     if (tma) {
         float4* o4 = reinterpret_cast<float4*>(xs);
         for (int j = tid; j < na * (kRow / 4); j += NT) {
             const int al = j / (kRow / 4), q = j - al * (kRow / 4);
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int w = 0; w < W; ++w) {
-                const int m = map[w * na + al];
-                if (m >= 0) {
-                    const float4 u = reinterpret_cast<const float4*>(acc + w * S96 + m)[q];
-                    v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
-                }
+            for (int e = pull_ptr[al]; e < pull_ptr[al + 1]; ++e) {
+                const int m = pull[e];
+                const float4 u = reinterpret_cast<const float4*>(acc + (m >> 16) * S96 + (m & 0xffff))[q];
+                v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
             }
             o4[j] = v;
         }
@@ -579,9 +592,9 @@ __global__ void __launch_bounds__(kMaxEnergyThreads) energy_fwd_kernel(const Ene
         for (int j = tid; j < na * per; j += NT) {
             const int al = j / per, rem = j - al * per;
             float v = 0.f;
-            for (int w = 0; w < W; ++w) {
-                const int m = map[w * na + al];
-                if (m >= 0) v += acc[w * S96 + m + rem];
+            for (int e = pull_ptr[al]; e < pull_ptr[al + 1]; ++e) {
+                const int m = pull[e];
+                v += acc[(m >> 16) * S96 + (m & 0xffff) + rem];
             }
             p.gradient[((int64_t)(a0 + al) * C + c0) * 3 + rem] = v;
         }

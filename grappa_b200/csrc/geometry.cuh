@@ -62,6 +62,27 @@ GHD void bond_geom(V3 p0, V3 p1, float& r, V3& g0) {
     g0 = inv * d;
 }
 
+// atan2(y, x) for y >= 0 (result in [0, pi]), branch-free: atan(t) on t = min/max in [0, 1] by an odd minimax
+// polynomial (degree 17, max abs error 1.0e-7 in fp32 evaluation), then the two reflections.  atan2(0, 0) = 0.
+GHD float atan2_pos(float y, float x) {
+    const float ax = fabsf(x);
+    const float lo = fminf(y, ax), hi = fmaxf(y, ax);
+    const float t = hi > 0.f ? lo * rcp_(hi) : 0.f;
+    const float s = t * t;
+    float p = 0.0024567246f;
+    p = fmaf(p, s, -0.014401359f);
+    p = fmaf(p, s, 0.039781228f);
+    p = fmaf(p, s, -0.07234858f);
+    p = fmaf(p, s, 0.10498947f);
+    p = fmaf(p, s, -0.14161229f);
+    p = fmaf(p, s, 0.19985907f);
+    p = fmaf(p, s, -0.33332598f);
+    p = fmaf(p, s, 0.99999988f);
+    p *= t;
+    p = y > ax ? 1.57079632679f - p : p;
+    return x < 0.f ? 3.14159265359f - p : p;
+}
+
 // theta in [0, pi]; g0 = dtheta/dx0, g2 = dtheta/dx2 (dtheta/dx1 = -(g0 + g2))
 GHD void angle_geom(V3 p0, V3 p1, V3 p2, float& theta, V3& g0, V3& g2) {
     V3 u = p0 - p1, v = p2 - p1;
@@ -69,7 +90,7 @@ GHD void angle_geom(V3 p0, V3 p1, V3 p2, float& theta, V3& g0, V3& g2) {
     float c2 = dot(c, c), uv = dot(u, v);
     float icn = c2 > kTiny ? rsqrt_(c2) : 0.f;
     float cn = c2 * icn;
-    theta = atan2f(cn, uv);
+    theta = atan2_pos(cn, uv);
     float u2 = dot(u, u), v2 = dot(v, v);
     float su = u2 > kTiny ? icn * rcp_(u2) : 0.f;
     float sv = v2 > kTiny ? icn * rcp_(v2) : 0.f;

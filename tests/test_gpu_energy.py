@@ -108,6 +108,40 @@ def test_energy_vjp_matches_double_backward():
             close(dleaf[l][key].grad, r, atol=3e-5 * float(r.abs().max()), msg=f"d{key} {l}")
 
 
+@pytest.mark.parametrize("n_parts", [1, 4, 7])
+def test_energy_matches_oracle_at_sweep_shape(n_parts):
+    """cfg-4 shape family (200 molecules x 500 conformations: 16 conformation chunks per molecule, TMA-staged rows)
+    against the oracle, element-wise, for several program partitions (warps per CTA)."""
+    g = S.cfg4_batch(n_mol=200, n_confs=500, seed=3)
+    params = random_params(g, seed=4)
+    ref = oracle_energy(g, params)
+    gd = g.to(DEV)
+    write_params(gd, params, DEV)
+    gd._plan_cache = {"plan": build_plan(g, n_parts=n_parts).to(DEV)}
+    out = Energy(materialize_tuple_terms=False)(gd)
+    escale = float(ref["energy"].abs().max())
+    close(out.nodes["g"].data["energy"], ref["energy"], atol=1e-5 * escale, msg="total energy")
+    for l, term in zip(LEVELS, ("bond", "angle", "proper", "improper")):
+        close(out.nodes["g"].data["energy_" + term], ref["term_energy"][l], atol=1e-5 * escale, msg="term energy " + term)
+    gscale = float(ref["gradient"].abs().max())
+    close(out.nodes["n1"].data["gradient"], ref["gradient"], atol=2e-5 * gscale, msg="gradient")
+
+
+def test_energy_unaligned_conformation_counts_match_aligned():
+    """C % 4 != 0 takes the coalesced-load path instead of the TMA rows: same numbers for the shared conformations."""
+    g = S.cfg4_batch(n_mol=3, n_confs=52, seed=5)
+    params = random_params(g, seed=6)
+    outs = {}
+    for C in (52, 50, 33, 1):
+        gd = g.to(DEV)
+        gd.nodes["n1"].data["xyz"] = gd.nodes["n1"].data["xyz"][:, :C].contiguous()
+        write_params(gd, params, DEV)
+        o = Energy(materialize_tuple_terms=False)(gd)
+        outs[C] = (o.nodes["g"].data["energy"].clone(), o.nodes["n1"].data["gradient"].clone())
+    for C in (50, 33, 1):
+        assert torch.equal(outs[C][0], outs[52][0][:, :C]) and torch.equal(outs[C][1], outs[52][1][:, :C])
+
+
 def test_energy_properties_full_size():
     """cfg 4 shape (scaled to 200 molecules x 500 conformations): determinism, translation invariance of energies,
     zero net force per molecule and conformation, linearity in the force constants."""

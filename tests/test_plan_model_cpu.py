@@ -79,8 +79,15 @@ def decode_energy_program(p, g):
         assert p0 % 4 == 0 and nw % 4 == 0
         pg = prog[p0:p0 + nw]
         offs = pg[:W + 1]
-        smap = pg[W + 1:W + 1 + W * na].reshape(W, na)
-        assert offs[0] == W + 1 + W * na and offs[-1] <= nw
+        pull_ptr = pg[W + 1:W + 2 + na]
+        pull = pg[W + 2 + na:W + 2 + na + pull_ptr[-1]]
+        assert pull_ptr[0] == 0 and (np.diff(pull_ptr) >= 0).all()
+        smap = np.full((W, na), -1, np.int64)                       # [part][atom] -> 96 * slot, from the pull lists
+        for al in range(na):
+            ent = pull[pull_ptr[al]:pull_ptr[al + 1]]
+            assert (np.diff(ent >> 16) > 0).all()                    # part order = summation order
+            smap[ent >> 16, al] = ent & 0xffff
+        assert offs[0] == W + 2 + na + pull_ptr[-1] and offs[-1] <= nw
         recs = []       # (part, level, tuple row, owner, atom rows)
         for w in range(W):
             pos = offs[w]
@@ -144,9 +151,9 @@ def test_energy_plan_invariants(block_atoms, n_parts):
             if owner:
                 owners[levels[level]][t] += 1
                 assert atom_blk[idx[0]] == b
-            per_kind[w] = per_kind.get(w, 0) + {0: 3, 1: 8, 2: 10, 3: 10}[level]
+            per_kind[w] = per_kind.get(w, 0) + {0: 6, 1: 14, 2: 18, 3: 18}[level]
         c = [per_kind.get(w, 0) for w in range(n_parts)]        # parts are balanced by estimated cost
-        assert max(c) - min(c) <= 20
+        assert max(c) - min(c) <= 36
     for li, l in enumerate(levels):
         assert (owners[l] == 1).all()       # every tuple's energy is counted exactly once
         idx = g.nodes[l].data["idxs"].numpy()
