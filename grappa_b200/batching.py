@@ -100,4 +100,11 @@ class DeviceBatch:
             raise ValueError("batch shapes differ from the static device buffers")
         self.fbuf.copy_(packed.fbuf, non_blocking=non_blocking)
         self.ibuf.copy_(packed.plan.host, non_blocking=non_blocking)
+        self.refresh_host_fields(packed)
         return self.graph
+
+    def refresh_host_fields(self, packed):
+        """The signature fixes totals and offsets, not the per-molecule split: host-side readers of
+        `g.batch_num_nodes()` / `plan.mol_atom_counts` (unbatching, per-molecule metrics) must see THIS batch's."""
+        self.graph._batch_num_nodes = {k: v.clone() for k, v in packed.batch_num_nodes.items()}
+        self.plan.mol_atom_counts = packed.plan.mol_atom_counts

@@ -449,33 +449,49 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
     return 0;
 }
 
+// The one place that decides how a column sum is laid out: which stage-1 kernel runs, into how many row chunks the
+// rows are cut, and therefore how many floats of partial sums stage 1 writes.  grappa_colsum launches from it,
+// grappa_colsum_noalloc checks its fixed array against it, grappa_colsum_scratch_floats reports its worst case.
+struct ColsumPlan {
+    bool vec;          // float4 path (16-byte aligned input, ldx % 4 == 0)
+    int64_t R;         // row chunks = rows of partial sums
+    int64_t floats;    // scratch floats touched: R * N
+};
+static ColsumPlan colsum_plan(int64_t M, int64_t N, const float* X, int64_t ldx) {
+    ColsumPlan p;
+    p.vec = ldx % 4 == 0 && al16(X);
+    p.R = p.vec ? col_chunks(M, N) : ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
+    p.floats = p.R * N;
+    return p;
+}
+
 extern "C" int64_t grappa_colsum_scratch_floats(int64_t M, int64_t N) {
-    return std::max(col_chunks(M, N), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * N;
+    return std::max(col_chunks(M, N), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * N;    // either path of colsum_plan
+}
+
+static int colsum_launch(const ColsumPlan& cp, int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch,
+                         cudaStream_t st) {
+    GRAPPA_CHECK_ARG(cp.R <= 65535, "too many rows for one launch");
+    if (cp.vec) {
+        ColArgs a = {};
+        a.M = M; a.N = N; a.X = X; a.ldx = ldx; a.part0 = scratch; a.rows_per_chunk = col_rows_per_chunk(M, N);
+        colreduce_vec_kernel<0><<<dim3((unsigned)ceil_div(N, 128), (unsigned)cp.R), 256, 0, st>>>(a);
+        GRAPPA_CHECK_LAUNCH();
+    } else {
+        dim3 grid((unsigned)ceil_div(N, 32), (unsigned)cp.R);
+        colreduce_stage1_kernel<0><<<grid, 256, 0, st>>>(M, N, X, ldx, nullptr, 0, nullptr, nullptr, scratch, nullptr);
+        GRAPPA_CHECK_LAUNCH();
+    }
+    colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(cp.R, N, scratch, nullptr, out, nullptr);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
 }
 
 extern "C" int grappa_colsum(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, float* scratch, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && N > 0, "bad sizes");
+    GRAPPA_CHECK_ARG(ldx >= N, "ldx must be >= N");
     GRAPPA_CHECK_ARG(X && out && scratch, "null pointer");
-    cudaStream_t st = (cudaStream_t)stream;
-    if (ldx % 4 == 0 && al16(X)) {
-        const int64_t R = col_chunks(M, N);
-        GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
-        ColArgs a = {};
-        a.M = M; a.N = N; a.X = X; a.ldx = ldx; a.part0 = scratch; a.rows_per_chunk = col_rows_per_chunk(M, N);
-        colreduce_vec_kernel<0><<<dim3((unsigned)ceil_div(N, 128), (unsigned)R), 256, 0, st>>>(a);
-        GRAPPA_CHECK_LAUNCH();
-        colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
-        GRAPPA_CHECK_LAUNCH();
-        return 0;
-    }
-    const int64_t R = ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk);
-    GRAPPA_CHECK_ARG(R <= 65535, "too many rows for one launch");
-    dim3 grid((unsigned)ceil_div(N, 32), (unsigned)R);
-    colreduce_stage1_kernel<0><<<grid, 256, 0, st>>>(M, N, X, ldx, nullptr, 0, nullptr, nullptr, scratch, nullptr);
-    GRAPPA_CHECK_LAUNCH();
-    colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(N, 32), 1), 256, 0, st>>>(R, N, scratch, nullptr, out, nullptr);
-    GRAPPA_CHECK_LAUNCH();
-    return 0;
+    return colsum_launch(colsum_plan(M, N, X, ldx), M, N, X, ldx, out, scratch, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------------- allocation-free column sum ---
@@ -506,9 +522,9 @@ static int noalloc_scratch(float** out) {
 extern "C" int grappa_colsum_noalloc(int64_t M, int64_t N, const float* X, int64_t ldx, float* out, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && N > 0, "bad sizes");
     GRAPPA_CHECK_ARG(X && out, "null pointer");
-    // exactly what grappa_colsum will touch: the float4 path (aligned input) uses far fewer row chunks than the fallback
-    const bool vec = ldx % 4 == 0 && al16(X);
-    const int64_t need = (vec ? col_chunks(M, N) : ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * N;
+    GRAPPA_CHECK_ARG(ldx >= N, "ldx must be >= N");
+    const ColsumPlan cp = colsum_plan(M, N, X, ldx);      // the same plan grappa_colsum launches from
+    const int64_t need = cp.floats;
     if (need > kNoAllocScratchFloats) {
         snprintf(g_err, sizeof(g_err),
                  "grappa_colsum_noalloc: a %lld x %lld column sum needs %lld floats of scratch but the built-in array holds %lld; "
@@ -519,7 +535,7 @@ extern "C" int grappa_colsum_noalloc(int64_t M, int64_t N, const float* X, int64
     float* scratch = nullptr;
     if (int rc = noalloc_scratch(&scratch)) return rc;
     // Nothing has to be cleared: stage 1 writes every partial that stage 2 reads, so leftovers of earlier calls are dead.
-    return grappa_colsum(M, N, X, ldx, out, scratch, stream);
+    return colsum_launch(cp, M, N, X, ldx, out, scratch, (cudaStream_t)stream);
 }
 
 extern "C" int grappa_epilogue_bwd(int64_t M, int64_t N, const float* dY, int64_t lddy, const float* Y, int64_t ldy,

@@ -650,10 +650,13 @@ static bool make_map(CUtensorMap* map, const float* base, int64_t rows, int64_t 
 template <bool A_MN, bool B_MN, bool B_PRE>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mblo, const GemmParams& p, cudaStream_t st,
                   float* workspace, int64_t workspace_floats) {
-    static bool configured = false;
-    if (!configured) {
+    // the opt-in shared-memory size is a per-DEVICE attribute of the kernel: one flag per device ordinal
+    static std::atomic<bool> configured[64];
+    int dev = 0;
+    GRAPPA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev].load(std::memory_order_acquire)) {
         GRAPPA_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<A_MN, B_MN, B_PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        configured = true;
+        if (dev >= 0 && dev < 64) configured[dev].store(true, std::memory_order_release);
     }
     const int64_t tiles = ceil_div(p.N, BN) * ceil_div(p.M, BM);
     const int nk = (int)ceil_div(p.K, BK);

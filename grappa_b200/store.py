@@ -346,6 +346,7 @@ class MoleculeStore:
         if batch.signature != spec.signature:
             raise ValueError("batch shapes differ from the static device buffers")
         self._stage(spec)
+        batch.refresh_host_fields(spec)
         L = _lib.lib()
         stream = torch.cuda.current_stream(self.device).cuda_stream
         seg, tab = self._dev_seg.data_ptr(), self._dev_tab.data_ptr()

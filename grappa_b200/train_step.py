@@ -86,8 +86,14 @@ class TrainStep:
                  energy_weight: float = 1.0, gradient_weight: float = 0.8, proper_regularisation: float = 1.0,
                  improper_regularisation: float = 1.0, world_size: int = 1, use_cuda_graph: bool = True,
                  process_group=None, overlap_comm: Optional[bool] = None, split_update: Optional[bool] = None,
-                 max_cached_shapes: int = 8):
+                 max_cached_shapes: int = 8, warmup_steps: int = 0):
+        """`warmup_steps`: linear learning-rate warm-up from 0 to `lr` over that many steps, as
+        training/lightning_model.py:136-161 (`_get_lr`; the reference's config uses 500; call `restart_warmup()` where
+        the reference re-arms it at a restart epoch, :199-201).  0 (default) = constant lr, which is what bench.py
+        times.  The epoch-level `lr_decay` of the reference's scheduler lives above this driver: assign `self.lr`."""
         self.device = ops.norm_device(device)
+        self.warmup_steps = int(warmup_steps)
+        self._warmup_step = 0 if self.warmup_steps > 0 else None
         self.model = model.to(self.device).train()
         self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
         self.flat = FlatParameters(self.model, self.device)
@@ -128,6 +134,15 @@ class TrainStep:
         self._loss_slot = 0
         self._works = []
         self._reduce_fn = None            # test hook: replaces the NCCL all-reduce of one bucket
+        # flat-buffer range of every writer's parameters: a writer that is skipped in forward (level absent or empty in
+        # this batch) never overwrites its gradient slices, which would otherwise still hold the LAST step's all-reduced
+        # sums when the exchange and AdamW run over the whole buffer -> cleared at the start of such a step
+        self._writer_ranges = {}
+        for lvl, prefix in (("n2", "parameter_writer.bond_writer."), ("n3", "parameter_writer.angle_writer."),
+                            ("n4", "parameter_writer.proper_writer."), ("n4_improper", "parameter_writer.improper_writer.")):
+            offs = [(self.flat.offsets[n], p.numel()) for n, p in self.flat.named if n.startswith(prefix)]
+            if offs:
+                self._writer_ranges[lvl] = (min(o for o, _ in offs), max(o + (k + 3) // 4 * 4 for o, k in offs))
         first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
         self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
         assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
@@ -147,6 +162,10 @@ class TrainStep:
         ops.WEIGHT_LO = self.flat.lo_of if ops.USE_WEIGHT_LO else None
         ops.DropoutSeeds.dev = self.seed_dev
         try:
+            plan = get_plan(g)
+            for lvl, (lo, hi) in self._writer_ranges.items():
+                if lvl not in g.ntypes or plan.T[lvl] == 0:
+                    self.flat.grads[lo:hi].zero_()          # (a memset node of the captured step)
             if self.overlap_comm:
                 plan = get_plan(g)
                 g = self.model.gnn(g, plan)
@@ -249,6 +268,7 @@ class TrainStep:
             stg["free"] = torch.cuda.Event()
             stg["free"].record(cur)
             st["prefetched"] = None
+            st["batch"].refresh_host_fields(packed)
         else:
             st["batch"].load(packed)
 
@@ -295,9 +315,24 @@ class TrainStep:
 
     def optimizer_step(self):
         self.t += 1
+        self._lr_now = self._next_lr()
         self._adamw_range(0, self.flat.numel)
         if self.split_update:
             self._writers_ready.record(torch.cuda.current_stream(self.device))
+
+    def restart_warmup(self):
+        self._warmup_step = 0 if self.warmup_steps > 0 else None
+
+    def _next_lr(self) -> float:
+        """lightning_model.py:136-153: the step counter advances once per optimisation step."""
+        if self._warmup_step is None:
+            return self.lr
+        if self._warmup_step >= self.warmup_steps:
+            self._warmup_step = None
+            return self.lr
+        lr = float(self._warmup_step) / self.warmup_steps * self.lr
+        self._warmup_step += 1
+        return lr
 
     def _adamw_range(self, lo: int, hi: int):
         f = self.flat
@@ -305,7 +340,7 @@ class TrainStep:
             return
         ptr = lambda t: t.data_ptr() + 4 * lo
         _lib.check(_lib.lib().grappa_adamw(hi - lo, ptr(f.params), ptr(f.grads), ptr(f.exp_avg), ptr(f.exp_avg_sq),
-                                           self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
+                                           self._lr_now, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
                                            getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
         ops.WEIGHT_EPOCH[0] += 1         # invalidates lo planes cached for use outside this driver
         if ops.USE_WEIGHT_LO:            # lo planes of the updated weights for the next step's GEMMs (B operand pre-split)
@@ -327,6 +362,7 @@ class TrainStep:
             w2 = dist.all_reduce(self.flat.grads[sp:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         self._grad_scale = 1.0 / self.world_size
         self.t += 1
+        self._lr_now = self._next_lr()
         self._upd_stream.wait_stream(cur)                       # gradients of this step are complete
         if w1 is not None:
             w1.wait()

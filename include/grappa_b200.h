@@ -10,9 +10,12 @@
  *   - plain pointers and sizes only; no torch types.  Unless a parameter is marked HOST it is a device pointer.
  *   - all floating point is fp32, indices are int32 on the device (the graph's int64 idxs are narrowed once by the
  *     host plan), row-major, leading dimensions in elements.
- *   - `stream` is a cudaStream_t passed as void*.  Calls are asynchronous on that stream and hold no global state.
+ *   - `stream` is a cudaStream_t passed as void*.  Calls are asynchronous on that stream and hold no global device
+ *     state -- with ONE exception, grappa_colsum_noalloc, whose scratch is a fixed array inside the library image
+ *     (shared by all its callers; see its declaration).
  *   - return value 0 = success; otherwise grappa_last_error() (thread-local) describes the failure.
- *   - nothing here allocates device memory: outputs and scratch are caller-provided.
+ *   - nothing here allocates device memory: outputs and scratch are caller-provided (grappa_colsum_noalloc brings its
+ *     scratch with the library instead of taking it from the caller; it does not allocate either).
  */
 #ifndef GRAPPA_B200_H
 #define GRAPPA_B200_H

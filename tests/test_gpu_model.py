@@ -147,6 +147,66 @@ def test_training_step_gradients_match_oracle_elementwise():
         np.testing.assert_allclose(p.grad.cpu().numpy(), r.numpy(), rtol=2e-3, atol=2e-4 * scale, err_msg=name)
 
 
+def test_training_step_at_the_benchmarked_size_matches_oracle():
+    """BASELINE.json configs[1] exactly as bench.py times it (32 molecules x 40 atoms x 50 conformations), dropout off:
+    loss, energies, forces at rtol 1e-4 and every parameter gradient against the CPU oracle."""
+    model, sd = build_model(train=True)
+    for m in model.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+    g = S.cfg2_batch(32, 50)
+    leaf = {k: (v.requires_grad_(True) if torch.is_floating_point(v) and not any(s in k for s in ("to_k.", "to_eq.", "k_mean", "k_std", "prefactors", "positional")) else v)
+            for k, v in sd.items()}
+    loss_ref, params_ref, en_ref = O.train_step_loss(leaf, g)
+    loss_ref.backward()
+    loss, gd = train_loss(model, g.to(DEV))
+    loss.backward()
+    np.testing.assert_allclose(loss.item(), loss_ref.item(), rtol=1e-4)
+    assert_params_close(graph_params(gd), params_ref, "cfg2")
+    e, er = gd.nodes["g"].data["energy"].detach().cpu().numpy(), en_ref["energy"].detach().numpy()
+    np.testing.assert_allclose(e, er, rtol=1e-4, atol=1e-5 * np.abs(er).max())
+    f, fr = gd.nodes["n1"].data["gradient"].detach().cpu().numpy(), en_ref["gradient"].detach().numpy()
+    np.testing.assert_allclose(f, fr, rtol=1e-4, atol=2e-5 * np.abs(fr).max())
+    for name, p in model.named_parameters():
+        r = leaf[name].grad
+        if r is None:
+            assert p.grad is None, name
+            continue
+        scale = float(r.abs().max())
+        np.testing.assert_allclose(p.grad.cpu().numpy(), r.numpy(), rtol=2e-3, atol=2e-4 * scale, err_msg=name)
+
+
+def test_skipped_writer_does_not_reapply_stale_gradients():
+    """A batch without impropers must not leave the previous step's improper-writer gradients in the flat buffer (they
+    would be all-reduced and applied again): step with impropers, then without, for eager and captured steps."""
+    from grappa_b200.batching import PackedBatch
+    from grappa_b200.train_step import TrainStep
+
+    def without_impropers(seed):
+        g = S.trimer_molecule(seed=seed, n_confs=3)
+        g.nodes["n4_improper"].data["idxs"] = torch.zeros((0, 4), dtype=torch.long)
+        g._num_nodes["n4_improper"] = 0
+        g._batch_num_nodes["n4_improper"] = torch.tensor([0])
+        return g
+
+    full = PackedBatch(batch([S.trimer_molecule(seed=s, n_confs=3) for s in (0, 1)]))
+    bare = PackedBatch(batch([without_impropers(s) for s in (0, 1)]))
+    for use_graph in (False, True):
+        model, _ = build_model(train=True)
+        ts = TrainStep(model, DEV, use_cuda_graph=use_graph, improper_regularisation=0.0)
+        lo, hi = ts._writer_ranges["n4_improper"]
+        for _ in range(5 if use_graph else 1):
+            ts.step(full)
+        assert float(ts.flat.grads[lo:hi].abs().max()) > 0
+        before = ts.flat.params[lo:hi].clone()
+        for _ in range(5 if use_graph else 1):
+            ts.step(bare)
+            assert float(ts.flat.grads[lo:hi].abs().max()) == 0.0, "stale improper-writer gradients survived"
+        ts.synchronize()
+        # with zero gradients the parameters only coast on Adam's momentum: bounded by lr per step
+        assert float((ts.flat.params[lo:hi] - before).abs().max()) <= 5 * ts.lr * 1.01
+
+
 def test_dropout_training_mode_runs_and_differs():
     model, _ = build_model(train=True)
     g = batch([S.trimer_molecule(seed=s, n_confs=2) for s in (0, 1)]).to(DEV)
