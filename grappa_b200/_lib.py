@@ -49,6 +49,9 @@ PROTOTYPES = {
     "grappa_energy_vjp": (I, [I64, P, P, P, P, P, I64, P, I64, P, I64, P, I64, P, P, P, P, P, I, P, I,
                               P, P, P, P, P, P, P]),
     "grappa_csr_build": (I, [I64, I64, P, P, P]),
+    "grappa_plan_build": (I, [I64, I64, P, P, P, P, P, I64, P, P, I, I, I, P, P, P, P]),
+    "grappa_plan_fill": (I, [P, P, I64]),
+    "grappa_plan_free": (None, [P]),
     "grappa_enumerate_tuples": (I, [I64, P, I64, P, P, P]),
     "grappa_pe_table_fwd": (I, [I64, I, I, P, I64, P, P]),
     "grappa_pe_table_bwd": (I, [I64, I, I, P, P, I64, P]),
@@ -136,7 +139,8 @@ class _ProfiledLib:
         fn = getattr(self._h, name)
         if not name.startswith("grappa_") or name in ("grappa_last_error", "grappa_launch_count", "grappa_abi_version",
                                                        "grappa_colsum_scratch_floats", "grappa_layernorm_bwd_scratch_floats",
-                                                       "grappa_csr_build", "grappa_energy_plan_build", "grappa_enumerate_tuples"):
+                                                       "grappa_csr_build", "grappa_energy_plan_build", "grappa_enumerate_tuples", "grappa_plan_build",
+                                                       "grappa_plan_fill", "grappa_plan_free"):
             return fn
         prof = self._p
 

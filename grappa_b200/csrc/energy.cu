@@ -17,6 +17,7 @@
 // Algorithmic HBM bytes per (molecule, conformation) with A atoms: 12A (xyz) + 12A (gradient) + 20 (energies).
 #include "common.cuh"
 #include "geometry.cuh"
+#include "energy_plan.h"
 #include <vector>
 #include <algorithm>
 #include <mutex>
@@ -66,15 +67,17 @@ struct PlanItem {
 
 using namespace grappa;
 
-extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
-                                        const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
-                                        const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
-                                        int block_atoms, int n_parts, int64_t* sizes_out,
-                                        int32_t* blk, int32_t* prog, int32_t* mol_tuple_off, int32_t* tuple_mol) {
+int grappa::build_energy_plan(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
+                              const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
+                              const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
+                              int block_atoms, int n_parts, bool fill, EnergyPlanOut& out) {
+    int64_t* sizes_out = out.sizes;
+    out.tuple_mol.assign((size_t)(T2 + T3 + T4 + T4i), 0);
+    int32_t* tuple_mol = out.tuple_mol.data();
     GRAPPA_CHECK_ARG(n_atoms >= 0 && n_mol >= 0, "bad sizes");
     GRAPPA_CHECK_ARG(block_atoms > 0 && block_atoms <= 128, "block_atoms must be in [1, 128]");
     GRAPPA_CHECK_ARG(n_parts >= 1 && n_parts <= kMaxParts, "n_parts must be in [1, 16]");
-    GRAPPA_CHECK_ARG(mol_atom_off != nullptr && sizes_out != nullptr, "null pointer");
+    GRAPPA_CHECK_ARG(mol_atom_off != nullptr, "null pointer");
     GRAPPA_CHECK_ARG(mol_atom_off[0] == 0 && mol_atom_off[n_mol] == n_atoms, "mol_atom_off must span [0, n_atoms]");
     LevelIdx lv[4] = {{idx2, T2, 2}, {idx3, T3, 3}, {idx4, T4, 4}, {idx4i, T4i, 4}};
     const int W = n_parts;
@@ -117,7 +120,7 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
             if (m < prev) return fail("grappa_energy_plan_build: %s tuple rows must be grouped by molecule in molecule order (row %lld)", "", (long long)t);
             prev = m;
             to[m + 1]++;
-            if (tuple_mol) tuple_mol[tuple_base + t] = m;
+            tuple_mol[tuple_base + t] = m;
         }
         for (int64_t m = 0; m < n_mol; ++m) { maxT[l] = std::max(maxT[l], to[m + 1]); to[m + 1] += to[m]; }
         tuple_base += lv[l].T;
@@ -198,8 +201,13 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
     sizes_out[4] = max_atoms; sizes_out[5] = any_multi; sizes_out[6] = W;
     for (int l = 0; l < 4; ++l) sizes_out[7 + l] = maxT[l];
     sizes_out[11] = any_nonlocal;
-    if (blk == nullptr) return 0;   // size query only
-    GRAPPA_CHECK_ARG(prog && mol_tuple_off, "null output array");
+    if (!fill) return 0;            // size query only
+    out.blk.assign((size_t)nB * kBlkStride, 0);
+    out.prog.assign((size_t)n_words, 0);
+    out.toff.assign(toff.size(), 0);
+    int32_t* blk = out.blk.data();
+    int32_t* prog = out.prog.data();
+    int32_t* mol_tuple_off = out.toff.data();
 
     for (size_t i = 0; i < toff.size(); ++i) mol_tuple_off[i] = (int32_t)toff[i];
     std::vector<int32_t> slot_of;
@@ -259,6 +267,25 @@ extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const in
         pg[W] = (int32_t)pos;
         while (pos < word0[b + 1] - word0[b]) pg[pos++] = 0;
     }
+    return 0;
+}
+
+extern "C" int grappa_energy_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
+                                        const int64_t* idx2, int64_t T2, const int64_t* idx3, int64_t T3,
+                                        const int64_t* idx4, int64_t T4, const int64_t* idx4i, int64_t T4i,
+                                        int block_atoms, int n_parts, int64_t* sizes_out,
+                                        int32_t* blk, int32_t* prog, int32_t* mol_tuple_off, int32_t* tuple_mol) {
+    GRAPPA_CHECK_ARG(sizes_out != nullptr, "null pointer");
+    GRAPPA_CHECK_ARG(blk == nullptr || (prog && mol_tuple_off), "null output array");
+    EnergyPlanOut out;
+    if (int rc = build_energy_plan(n_atoms, n_mol, mol_atom_off, idx2, T2, idx3, T3, idx4, T4, idx4i, T4i, block_atoms, n_parts,
+                                   blk != nullptr, out)) return rc;
+    for (int i = 0; i < 12; ++i) sizes_out[i] = out.sizes[i];
+    if (blk == nullptr) return 0;   // size query only
+    std::copy(out.blk.begin(), out.blk.end(), blk);
+    std::copy(out.prog.begin(), out.prog.end(), prog);
+    std::copy(out.toff.begin(), out.toff.end(), mol_tuple_off);
+    if (tuple_mol) std::copy(out.tuple_mol.begin(), out.tuple_mol.end(), tuple_mol);
     return 0;
 }
 

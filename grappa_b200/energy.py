@@ -13,7 +13,7 @@ Same constructor keywords, same graph reads (`xyz`, `idxs`, `k`/`eq` + suffix) a
 import torch
 
 from . import ops
-from .plan import get_plan
+from .plan import ensure_energy, get_plan
 
 _LEVELS = ("n2", "n3", "n4", "n4_improper")
 
@@ -45,7 +45,7 @@ class Energy(torch.nn.Module):
         if "xyz" not in n1.keys():
             raise ValueError("xyz coordinates must be stored in g.nodes['n1'].data['xyz']")
         xyz = n1["xyz"]
-        plan = get_plan(g)
+        plan = ensure_energy(g, get_plan(g))
         params = {}
         mask = 0
         for term in self.terms:

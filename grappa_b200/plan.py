@@ -53,17 +53,24 @@ class BatchPlan:
         self.host: Optional[torch.Tensor] = None
         self.dev: Optional[torch.Tensor] = None
         self.mol_atom_counts = None
+        self.ext: Optional["BatchPlan"] = None  # energy sections added after the fact (ensure_energy)
 
     # -- access -------------------------------------------------------------------------------------------------
     def view(self, name: str) -> torch.Tensor:
+        if name not in self.offsets and self.ext is not None:
+            return self.ext.view(name)
         s, n = self.offsets[name]
         return self.dev[s:s + n]
 
     def ptr(self, name: str) -> int:
+        if name not in self.offsets and self.ext is not None:
+            return self.ext.ptr(name)
         s, n = self.offsets[name]
         return self.dev.data_ptr() + 4 * s
 
     def host_view(self, name: str) -> np.ndarray:
+        if name not in self.offsets and self.ext is not None:
+            return self.ext.host_view(name)
         s, n = self.offsets[name]
         return self.host.numpy()[s:s + n]
 
@@ -76,6 +83,8 @@ class BatchPlan:
         out = BatchPlan()
         out.__dict__.update(self.__dict__)
         out.dev = self.host.to(device, non_blocking=non_blocking)
+        if self.ext is not None:
+            out.ext = self.ext.to(device, non_blocking=non_blocking)
         return out
 
     def pin_memory(self) -> "BatchPlan":
@@ -97,110 +106,153 @@ class BatchPlan:
         return int(self.host.numel()) * 4
 
 
-def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] = None) -> BatchPlan:
+# section order of grappa_plan_build (csrc/plan.cu)
+def _section_names():
+    names = []
+    for lvl in LEVELS:
+        names += [f"idx_{lvl}", f"inc_ptr_{lvl}", f"inc_tok_{lvl}", f"tab_idx_{lvl}", f"tab_ptr_{lvl}", f"tab_tok_{lvl}"]
+    names += ["in_ptr", "in_nbr", "out_ptr", "out_nbr", "e_blk", "e_prog", "e_mol_toff", "tuple_mol", "mol_atom_off"]
+    names += [f"mol_off_{lvl}" for lvl in LEVELS]
+    return names
+
+
+SECTION_NAMES = _section_names()
+_ENERGY_SECTIONS = ("e_blk", "e_prog", "e_mol_toff", "tuple_mol")
+
+
+def _host_i64(t) -> np.ndarray:
+    return np.ascontiguousarray(t.detach().to("cpu", torch.int64).contiguous().numpy())
+
+
+def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] = None, energy: Optional[bool] = None,
+               pin: bool = False) -> BatchPlan:
+    """One call into grappa_plan_build.  `energy`: include the energy kernel's plan (default: iff the graph carries
+    conformations, i.e. `xyz`; Energy.forward adds it lazily otherwise, so parameter-only inference does not pay for it).
+    `pin`: the packed buffer is written straight into pinned host memory."""
     L = _lib.lib()
     p = BatchPlan()
     n_atoms = int(g.num_nodes("n1"))
     p.n_atoms = n_atoms
-    bnn = g.batch_num_nodes("n1").to("cpu", torch.int64).numpy()
+    bnn = _host_i64(g.batch_num_nodes("n1"))
     p.n_mol = int(len(bnn))
     p.mol_atom_counts = bnn
     mol_atom_off = np.zeros(p.n_mol + 1, np.int64)
     np.cumsum(bnn, out=mol_atom_off[1:])
     if int(mol_atom_off[-1]) != n_atoms:
         raise AssertionError("batch_num_nodes('n1') does not sum to the number of atoms")
-
-    arrays: Dict[str, np.ndarray] = {}
-    idx64: Dict[str, np.ndarray] = {}
-    present = []
-    for lvl in LEVELS:
-        if lvl in g.ntypes:
-            present.append(lvl)
-            ix = g.nodes[lvl].data["idxs"]
-            ix = ix.detach().to("cpu", torch.int64).contiguous().numpy().reshape(-1, N_SEQ[lvl])
-            if ix.size:
-                mx, mn = int(ix.max()), int(ix.min())
-                # reference: models/grappa.py:179-185 (AssertionError on out-of-range idxs)
-                assert mx < n_atoms and mn >= 0, (
-                    f'Encountered idxs up to {mx} at the level g.nodes[{lvl}].data["idxs"], but there are only '
-                    f'{n_atoms} atom-level-nodes in the graph')
-        else:
-            ix = np.zeros((0, N_SEQ[lvl]), np.int64)
-        idx64[lvl] = ix
-        p.T[lvl] = int(ix.shape[0])
-        arrays["idx_" + lvl] = ix.astype(np.int32).reshape(-1)
-        # atom -> token rows (row = t * n_seq + i), stable in row order
-        inc_ptr = np.zeros(n_atoms + 1, np.int32)
-        inc_tok = np.zeros(ix.size, np.int32)
-        _lib.check(L.grappa_csr_build(ix.size, n_atoms, _np_ptr(np.ascontiguousarray(ix.reshape(-1))), _np_ptr(inc_ptr),
-                                      _np_ptr(inc_tok)))
-        arrays["inc_ptr_" + lvl] = inc_ptr
-        arrays["inc_tok_" + lvl] = inc_tok
-        if lvl in PE_PATTERN:
-            # table row of a token = 2 * atom + pe(position): composes under batching with the offset 2 * atom_offset
-            keys = np.ascontiguousarray((2 * ix + np.asarray(PE_PATTERN[lvl], np.int64)[None, :]).reshape(-1))
-            tab_ptr = np.zeros(2 * n_atoms + 1, np.int32)
-            tab_tok = np.zeros(ix.size, np.int32)
-            _lib.check(L.grappa_csr_build(ix.size, 2 * n_atoms, _np_ptr(keys), _np_ptr(tab_ptr), _np_ptr(tab_tok)))
-            arrays["tab_idx_" + lvl] = keys.astype(np.int32)
-            arrays["tab_ptr_" + lvl] = tab_ptr
-            arrays["tab_tok_" + lvl] = tab_tok
-    p.levels_present = tuple(present)
-
-    # bond edges -> CSR by destination / by source
-    src, dst = get_bond_edges(g)
-    src = src.detach().to("cpu", torch.int64).contiguous().numpy()
-    dst = dst.detach().to("cpu", torch.int64).contiguous().numpy()
-    p.n_edges = int(len(src))
-    for name, key, other in (("in", dst, src), ("out", src, dst)):
-        ptr = np.zeros(n_atoms + 1, np.int32)
-        order = np.zeros(len(key), np.int32)
-        _lib.check(L.grappa_csr_build(len(key), n_atoms, _np_ptr(key), _np_ptr(ptr), _np_ptr(order)))
-        arrays[name + "_ptr"] = ptr
-        arrays[name + "_nbr"] = other[order].astype(np.int32)
-
-    # energy plan
-    sizes = np.zeros(12, np.int64)
-    args_idx = []
-    keep = []
-    for lvl in LEVELS:
-        a = np.ascontiguousarray(idx64[lvl].reshape(-1))
-        args_idx += [_np_ptr(a), p.T[lvl]]
-        keep.append(a)   # keep alive until the second call
+    if energy is None:
+        energy = "xyz" in g.nodes["n1"].data
     if n_parts is None:
         n_parts = int(os.environ.get("GRAPPA_ENERGY_PARTS", ENERGY_PARTS))
-    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, n_parts,
-                                          _np_ptr(sizes), None, None, None, None))
-    nB, nW = int(sizes[0]), int(sizes[1])
-    blk = np.zeros(nB * 12, np.int32)
-    prog = np.zeros(nW, np.int32)
-    mol_toff = np.zeros(4 * (p.n_mol + 1), np.int32)
-    tuple_mol = np.zeros(sum(p.T.values()), np.int32)
-    _lib.check(L.grappa_energy_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), *args_idx, block_atoms, n_parts,
-                                          _np_ptr(sizes), _np_ptr(blk), _np_ptr(prog), _np_ptr(mol_toff), _np_ptr(tuple_mol)))
-    del keep
-    p.energy_sizes = dict(zip(ENERGY_SIZE_KEYS, (int(v) for v in sizes)))
-    arrays.update(e_blk=blk, e_prog=prog, e_mol_toff=mol_toff, tuple_mol=tuple_mol)
 
-    # per-molecule offsets (int32) for the fused loss / segmenting
-    arrays["mol_atom_off"] = mol_atom_off.astype(np.int32)
-    for lvl in LEVELS:
-        off = np.zeros(p.n_mol + 1, np.int64)
+    keep = []
+    idx_ptrs = (ctypes.c_void_p * 4)()
+    cnt_ptrs = (ctypes.c_void_p * 4)()
+    pe_ptrs = (ctypes.c_void_p * 4)()
+    T = (ctypes.c_int64 * 4)()
+    present = []
+    for i, lvl in enumerate(LEVELS):
         if lvl in g.ntypes:
-            np.cumsum(g.batch_num_nodes(lvl).to("cpu", torch.int64).numpy(), out=off[1:])
-        arrays["mol_off_" + lvl] = off.astype(np.int32)
+            present.append(lvl)
+            ix = _host_i64(g.nodes[lvl].data["idxs"]).reshape(-1, N_SEQ[lvl])
+            cnt = _host_i64(g.batch_num_nodes(lvl))
+            keep += [ix, cnt]
+            idx_ptrs[i] = ix.ctypes.data if ix.size else None
+            cnt_ptrs[i] = cnt.ctypes.data
+            T[i] = ix.shape[0]
+        else:
+            idx_ptrs[i], cnt_ptrs[i], T[i] = None, None, 0
+        p.T[lvl] = int(T[i])
+        if lvl in PE_PATTERN:
+            pat = np.asarray(PE_PATTERN[lvl], np.int32)
+            keep.append(pat)
+            pe_ptrs[i] = pat.ctypes.data
+        else:
+            pe_ptrs[i] = None
+    p.levels_present = tuple(present)
+    src, dst = get_bond_edges(g)
+    src, dst = _host_i64(src), _host_i64(dst)
+    p.n_edges = int(len(src))
 
-    # pack (16-byte aligned sections)
+    n_out = ctypes.c_int64(0)
+    sections = np.zeros(2 * len(SECTION_NAMES), np.int64)
+    sizes = np.zeros(12, np.int64)
+    handle = ctypes.c_void_p(None)
+    rc = L.grappa_plan_build(n_atoms, p.n_mol, _np_ptr(mol_atom_off), idx_ptrs, T, cnt_ptrs, pe_ptrs, p.n_edges,
+                             _np_ptr(src) if p.n_edges else None, _np_ptr(dst) if p.n_edges else None,
+                             1 if energy else 0, block_atoms, n_parts, ctypes.byref(n_out), _np_ptr(sections), _np_ptr(sizes),
+                             ctypes.byref(handle))
+    if rc == 4:       # reference: models/grappa.py:179-185 (AssertionError on out-of-range idxs)
+        msg = L.grappa_last_error().decode()
+        for i, lvl in enumerate(LEVELS):
+            msg = msg.replace(f"at the level {i},", f'at the level g.nodes[{lvl}].data["idxs"],')
+        raise AssertionError(msg)
+    _lib.check(rc)
+    try:
+        host = torch.empty(int(n_out.value), dtype=torch.int32, pin_memory=bool(pin and torch.cuda.is_available()))
+        _lib.check(L.grappa_plan_fill(handle, host.data_ptr(), int(n_out.value)))
+    finally:
+        L.grappa_plan_free(handle)
+    for i, name in enumerate(SECTION_NAMES):
+        if name in _ENERGY_SECTIONS and not energy:
+            continue
+        if name.startswith("tab_") and name.split("_", 2)[2] not in PE_PATTERN:
+            continue
+        p.offsets[name] = (int(sections[2 * i]), int(sections[2 * i + 1]))
+    p.energy_sizes = dict(zip(ENERGY_SIZE_KEYS, (int(v) for v in sizes))) if energy else None
+    p.host = host
+    del keep
+    return p
+
+
+def build_energy_ext(g, plan: BatchPlan, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] = None) -> BatchPlan:
+    """The energy kernel's plan alone, for a graph whose batch plan was built without it (parameter-only inference that
+    later evaluates energies): its own small packed buffer, attached to `plan` as `plan.ext`."""
+    L = _lib.lib()
+    if n_parts is None:
+        n_parts = int(os.environ.get("GRAPPA_ENERGY_PARTS", ENERGY_PARTS))
+    mol_atom_off = np.zeros(plan.n_mol + 1, np.int64)
+    np.cumsum(np.asarray(plan.mol_atom_counts, np.int64), out=mol_atom_off[1:])
+    args, keep = [], []
+    for lvl in LEVELS:
+        if lvl in g.ntypes:
+            a = _host_i64(g.nodes[lvl].data["idxs"]).reshape(-1)
+        else:
+            a = np.zeros(0, np.int64)
+        keep.append(a)
+        args += [_np_ptr(a), plan.T[lvl]]
+    sizes = np.zeros(12, np.int64)
+    _lib.check(L.grappa_energy_plan_build(plan.n_atoms, plan.n_mol, _np_ptr(mol_atom_off), *args, block_atoms, n_parts,
+                                          _np_ptr(sizes), None, None, None, None))
+    arrays = dict(e_blk=np.zeros(int(sizes[0]) * 12, np.int32), e_prog=np.zeros(int(sizes[1]), np.int32),
+                  e_mol_toff=np.zeros(4 * (plan.n_mol + 1), np.int32), tuple_mol=np.zeros(sum(plan.T.values()), np.int32))
+    _lib.check(L.grappa_energy_plan_build(plan.n_atoms, plan.n_mol, _np_ptr(mol_atom_off), *args, block_atoms, n_parts,
+                                          _np_ptr(sizes), _np_ptr(arrays["e_blk"]), _np_ptr(arrays["e_prog"]),
+                                          _np_ptr(arrays["e_mol_toff"]), _np_ptr(arrays["tuple_mol"])))
+    ext = BatchPlan()
     total = 0
     for k, a in arrays.items():
-        p.offsets[k] = (total, int(a.size))
+        ext.offsets[k] = (total, int(a.size))
         total += (int(a.size) + 3) // 4 * 4
     buf = np.zeros(max(total, 4), np.int32)
     for k, a in arrays.items():
-        s, n = p.offsets[k]
-        buf[s:s + n] = a
-    p.host = torch.from_numpy(buf)
-    return p
+        s0, n = ext.offsets[k]
+        buf[s0:s0 + n] = a
+    ext.host = torch.from_numpy(buf)
+    ext.energy_sizes = dict(zip(ENERGY_SIZE_KEYS, (int(v) for v in sizes)))
+    return ext
+
+
+def ensure_energy(g, plan: BatchPlan) -> BatchPlan:
+    """Makes sure `plan` can serve the energy kernel (Energy.forward calls this)."""
+    if plan.energy_sizes is not None:
+        return plan
+    ext = build_energy_ext(g, plan)
+    if plan.dev is not None:
+        ext = ext.to(plan.dev.device)
+    plan.ext = ext
+    plan.energy_sizes = ext.energy_sizes
+    return plan
 
 
 def get_plan(g, device=None) -> BatchPlan:

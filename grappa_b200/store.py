@@ -102,7 +102,7 @@ class MoleculeStore:
         for m, g in enumerate(mols):
             if list(g.ntypes) != self.ntypes:
                 raise ValueError("all molecules of a store must have the same node types")
-            plan = build_plan(g)
+            plan = build_plan(g, energy=True)
             if plan.n_mol != 1:
                 raise ValueError("store entries must be single molecules")
             if self.int_names is None:

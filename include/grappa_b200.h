@@ -258,6 +258,26 @@ int grappa_energy_vjp(int64_t C, const float* xyz, const float* gE, const float*
  * their original order.  Used for CSR-by-destination / by-source of the bond edges and the atom -> token incidence. */
 int grappa_csr_build(int64_t n, int64_t n_keys, const int64_t* keys, int32_t* ptr, int32_t* order);
 
+/* The whole host batch plan behind one call (HOST pointers only): idxs narrowed to int32, atom -> token incidence CSRs,
+ * (atom, positional-encoding) token tables, bond-edge CSRs by destination / source, optionally the energy plan, and the
+ * per-molecule offsets, as sections of ONE packed int32 buffer that reaches the device in a single copy.  Replaces what
+ * the reference re-derives on every call by advanced indexing and DGL segment bookkeeping
+ * (models/interaction_parameters.py:184, models/internal_coordinates.py:31-94, models/energy.py:69) and performs the
+ * idxs bounds check of models/grappa.py:179-185 (return code 4, message in that wording).
+ *   idx[l] (T[l], n_seq) int64 for l = n2, n3, n4, n4_improper; level_counts[l] (n_mol) tuples per molecule or NULL (level
+ *   absent); pe_pattern[l] (n_seq) positional-encoding value per tuple position or NULL (no token table for that level).
+ * Outputs: *n_int32_out = buffer length; sections_out[2 * i] / [2 * i + 1] = offset / length (int32 elements) of section
+ * i in the order listed in csrc/plan.cu (37 sections; absent ones have length 0); energy_sizes_out[12] as
+ * grappa_energy_plan_build (only with_energy); *handle_out owns the packed buffer until grappa_plan_fill copies it into
+ * caller memory (pinned, typically) and grappa_plan_free releases it. */
+int grappa_plan_build(int64_t n_atoms, int64_t n_mol, const int64_t* mol_atom_off,
+                      const int64_t* const* idx, const int64_t* T, const int64_t* const* level_counts,
+                      const int32_t* const* pe_pattern, int64_t n_edges, const int64_t* edge_src, const int64_t* edge_dst,
+                      int with_energy, int block_atoms, int n_parts,
+                      int64_t* n_int32_out, int64_t* sections_out, int64_t* energy_sizes_out, void** handle_out);
+int grappa_plan_fill(void* handle, int32_t* out, int64_t n_int32);
+void grappa_plan_free(void* handle);
+
 /* Interaction-tuple enumeration from the bond list; replaces utils/tuple_indices.py:8-70 (get_idx_tuples) and
  * :73-110 (get_neighbor_dict).  bonds: (n_bonds,2) int64 atom rows in [0,n_atoms).  Rows come out in the reference's
  * order: outer loop over atoms in first-appearance order of the flattened bond list, sorted neighbour lists, angle
