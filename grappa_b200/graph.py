@@ -87,12 +87,26 @@ class HeteroGraph:
         return self._edges.device
 
     def to(self, device, non_blocking: bool = False) -> "HeteroGraph":
+        if torch.device(device).type == "cuda" and self.device.type == "cpu" and "plan" not in self._plan_cache \
+                and "n1" in self._num_nodes:
+            # host -> device (the `g.to(device)` of grappa.py:67): build the batch plan now, from the host-resident index
+            # tensors, so that it travels with the graph instead of being derived from device copies (a read-back)
+            # (attached to the device copy only: the host graph stays free to be edited)
+            try:
+                from .plan import build_plan
+                fresh_plan = build_plan(self)
+            except Exception:
+                fresh_plan = None            # malformed graphs raise where the reference raises: in the model's forward
+        else:
+            fresh_plan = None
         g = HeteroGraph(self._num_nodes, self._edges.to(device, non_blocking=non_blocking), self._batch_num_nodes)
         for nt, d in self._ndata.items():
             for k, v in d.items():
                 g._ndata[nt][k] = v.to(device, non_blocking=non_blocking)
         # plans built from host-side index tensors travel with the graph
         g._plan_cache = {k: (p.to(device) if hasattr(p, "to") else p) for k, p in self._plan_cache.items()}
+        if fresh_plan is not None:
+            g._plan_cache["plan"] = fresh_plan.to(device)
         return g
 
     def pin_memory(self) -> "HeteroGraph":

@@ -143,7 +143,14 @@ def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] 
     if energy is None:
         energy = "xyz" in g.nodes["n1"].data
     if n_parts is None:
-        n_parts = int(os.environ.get("GRAPPA_ENERGY_PARTS", ENERGY_PARTS))
+        n_parts = int(os.environ.get("GRAPPA_ENERGY_PARTS", 0))
+    if n_parts <= 0:
+        # warps per CTA of the energy kernel: 4 is best once the grid fills the machine (cfg 4: 16,000 CTAs); a training
+        # batch has few (molecule, conformation-chunk) CTAs, each latency-bound, so it is cut into more, shorter parts
+        n_parts = ENERGY_PARTS
+        if energy and "xyz" in g.nodes["n1"].data:
+            ctas = p.n_mol * ((int(g.nodes["n1"].data["xyz"].shape[1]) + 31) // 32)
+            n_parts = ENERGY_PARTS if ctas >= 600 else (8 if ctas >= 150 else 16)
 
     keep = []
     idx_ptrs = (ctypes.c_void_p * 4)()

@@ -64,7 +64,10 @@ class CollatedSpec:
 
 
 class MoleculeStore:
-    def __init__(self, molecules: Sequence[HeteroGraph], device, feature_names: Optional[List[str]] = None):
+    def __init__(self, molecules: Sequence[HeteroGraph], device, feature_names: Optional[List[str]] = None,
+                 energy_parts: int = 16):
+        """`energy_parts`: warps per CTA of the energy kernel for batches collated from this store (every molecule's
+        plan is compiled for it; training batches have few CTAs, hence many short parts: plan.build_plan)."""
         if len(molecules) == 0:
             raise ValueError("empty molecule store")
         self.device = torch.device(device)
@@ -102,7 +105,7 @@ class MoleculeStore:
         for m, g in enumerate(mols):
             if list(g.ntypes) != self.ntypes:
                 raise ValueError("all molecules of a store must have the same node types")
-            plan = build_plan(g, energy=True)
+            plan = build_plan(g, energy=True, n_parts=energy_parts)
             if plan.n_mol != 1:
                 raise ValueError("store entries must be single molecules")
             if self.int_names is None:

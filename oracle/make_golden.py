@@ -6,6 +6,7 @@ TEST INFRASTRUCTURE.  Generates tests/golden/*.npz|json by running the UNMODIFIE
 
 Fixtures:
   state_dict_layout.json   key -> [shape, dtype] of GrappaModel(**configs/model/default.yaml).state_dict()
+  state_dict_constants.npz the non-learnable buffers of that state dict (statistics, permutations, encodings)
   cfg1_forward.npz         22-atom ACE-ALA-NME, 5 confs: inputs, h, k/eq per level, internal coordinates,
                            per-tuple / per-term / total energies, dE/dxyz  (dihedral noise zeroed)
   batch3_train.npz         3 x 40-atom molecules x 4 confs batched with the reference's dgl_utils.batch:
@@ -84,6 +85,13 @@ def main():
     sd = model.state_dict()
     with open(os.path.join(OUT, "state_dict_layout.json"), "w") as f:
         json.dump({k: [list(v.shape), str(v.dtype)] for k, v in sd.items()}, f, indent=0)
+    # the buffers that deterministic_fill_ leaves alone (parameter statistics, permutations, positional encodings ...):
+    # with them and the layout a state dict can be rebuilt anywhere without the reference or the product's model code
+    from weights import _KEEP
+    np.savez_compressed(os.path.join(OUT, "state_dict_constants.npz"),
+                        **{k: v.numpy() for k, v in sd.items() if not torch.is_floating_point(v) or any(c in k for c in _KEEP)})
+    if "--constants-only" in sys.argv:
+        return
     deterministic_fill_(sd)
     model.load_state_dict(sd)
 
