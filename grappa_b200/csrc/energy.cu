@@ -187,7 +187,8 @@ int grappa::build_energy_plan(int64_t n_atoms, int64_t n_mol, const int64_t* mol
             n_pull[b] = W * blocks[b].na;
         }
         w += n_pull[b];
-        w = (w + 3) / 4 * 4;
+        w = (w + 63) / 64 * 64;     // coarse granularity: similar molecules get equal program sizes, so batches drawn from
+                                    // them keep one buffer layout (= one captured step graph)
         word0[b + 1] = word0[b] + w;
         max_words = std::max(max_words, w);
         max_atoms = std::max<int64_t>(max_atoms, blocks[b].na);
