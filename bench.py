@@ -302,7 +302,7 @@ def main():
             "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": mols, "parallelism": f"dp{world}",
-                       "gemm_math": "fp32 FFMA" if ops.MATH_MODE == 0 else "tcgen05 3xTF32",
+                       "gemm_math": {0: "fp32 FFMA", 1: "tcgen05 3xTF32", 2: "tcgen05 bf16x3 (forward, dX) + 3xTF32 (dW)"}[ops.MATH_MODE],
                        "cuda_graph": not args.no_graph,
                        "l2": "no explicit flush: one step touches parameters + gradients + Adam state (4 x 83 MB) plus "
                              "~0.5 GB of activations, several times the 126 MB L2"},
@@ -335,9 +335,9 @@ def main():
         _lib.profiler = None
         ts.use_cuda_graph = ts_graph
         # device time per entry point: its recorded launches replayed back to back in one CUDA graph (CUDA events)
-        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex"}     # one kernel family: one roofline entry
+        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"}     # one kernel family: one roofline entry
         summ.setdefault("grappa_gemm", {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
-        for other in ("grappa_gemm_actgrad", "grappa_gemm_ex"):
+        for other in ("grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"):
             if other in summ:
                 extra_g = summ.pop(other)
                 for k2 in ("calls", "ms", "flops"):
@@ -350,7 +350,7 @@ def main():
         gemm_ms = dev_ms["grappa_gemm"]
         tf = gm["flops"] / (gemm_ms * 1e-3) / 1e12
         peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-        line["roofline"] = {"kernel": ("gemm_tc_kernel" if ops.MATH_MODE == 1 else "sgemm_kernel") +
+        line["roofline"] = {"kernel": {0: "sgemm_kernel", 1: "gemm_tc_kernel", 2: "gemm_bf16_kernel + gemm_tc_kernel"}[ops.MATH_MODE] +
                                       " (grappa_gemm: all dense layers fwd+bwd, fused bias/ELU/dropout/residual epilogue)",
                             "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
                             "frac_of_3xtf32_ceiling": tf / (peak_tf / 6.0),
@@ -373,12 +373,13 @@ def main():
         # The weight-gradient GEMMs are issued on low-priority side streams with a CTA budget (un-split: 4-64 CTAs
         # each) so that they run UNDER the activation-gradient chains; replayed alone and serially they look slow by
         # construction.  Both classes are reported; `achieved` above is over all launches, as the contract defines it.
-        is_bg = lambda n, a: n in ("grappa_gemm", "grappa_gemm_ex") and ((a[19] >> 16) & 1) == 1
+        is_bg = lambda n, a: n in ("grappa_gemm", "grappa_gemm_ex", "grappa_gemm_bf16x3") and ((a[19] >> 16) & 1) == 1
+        mnk = lambda n, a: (a[0], a[1], a[2]) if n == "grappa_gemm_bf16x3" else (a[1], a[2], a[3])
         fl = {"foreground": [0.0, 0], "background": [0.0, 0]}
         for n, _, _, a in prof.records:
             if n in gemm_names:
                 c = fl["background" if is_bg(n, a) else "foreground"]
-                c[0] += 2.0 * a[1] * a[2] * a[3]
+                c[0] += 2.0 * mnk(n, a)[0] * mnk(n, a)[1] * mnk(n, a)[2]
                 c[1] += 1
         for cls, keep in (("foreground", lambda n, a: not is_bg(n, a)), ("background", is_bg)):
             ms_c = prof.replay_ms(gemm_names, keep=keep)

@@ -23,6 +23,9 @@ PROTOTYPES = {
     "grappa_gemm_actgrad": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I64, I, P, I64, P]),
     "grappa_gemm_ex": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P, P]),
     "grappa_split_lo": (I, [I64, P, P, P]),
+    "grappa_gemm_bf16x3": (I, [I64, I64, I64, P, I64, P, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P]),
+    "grappa_split_bf16_elems": (I64, [I64, I64]),
+    "grappa_split_bf16": (I, [I64, P, I64, P, P, P]),
     "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P, P, P]),
     "grappa_colsum_scratch_floats": (I64, [I64, I64]),
     "grappa_colsum": (I, [I64, I64, P, I64, P, P, P]),
@@ -88,6 +91,8 @@ class Profiler:
             d["ms"] += a.elapsed_time(b)
             if name in ("grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex"):
                 d["flops"] += 2.0 * args[1] * args[2] * args[3]
+            elif name == "grappa_gemm_bf16x3":
+                d["flops"] += 2.0 * args[0] * args[1] * args[2]
             elif name == "grappa_energy_fwd":                      # 24 B per atom-conformation + 20 B per molecule-conformation
                 d["bytes"] += args[2] * (24.0 * args[0] + 20.0 * args[1])
             elif name == "grappa_energy_vjp":

@@ -288,3 +288,30 @@ extern "C" int grappa_gemm_ex(int layout, int64_t M, int64_t N, int64_t K,
     return gemm_impl(layout, M, N, K, A, lda, B, ldb, C, ldc, bias, act, res1, ldr1, res2, ldr2, drop_p, seed, seed_dev, math_mode,
                      workspace, workspace_floats, stream, elu_out, ld_eo, B_lo);
 }
+
+extern "C" int grappa_gemm_bf16x3(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda,
+                                  const uint16_t* B_hi, const uint16_t* B_lo, int64_t ldb16, float* C, int64_t ldc,
+                                  const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                                  float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                                  float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo, void* stream) {
+    GRAPPA_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "negative size");
+    GRAPPA_CHECK_ARG(act == 0 || act == 1, "act must be 0 (none) or 1 (ELU)");
+    GRAPPA_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "drop_p must be in [0,1)");
+    GRAPPA_CHECK_ARG(elu_out == nullptr || ld_eo >= N, "ld_eo must be >= N");
+    if (M == 0 || N == 0) return 0;
+    GRAPPA_CHECK_ARG(A && B_hi && B_lo && C, "null matrix pointer");
+    GRAPPA_CHECK_ARG(aligned16(A) && lda % 4 == 0 && aligned16(B_hi) && aligned16(B_lo) && ldb16 % 8 == 0 && ldb16 >= K,
+                     "A must be 16-byte aligned with lda % 4 == 0; the planes 16-byte aligned with ldb16 % 8 == 0, ldb16 >= K");
+    GRAPPA_CHECK_ARG(M >= 32 && N >= 32 && K >= 32, "shapes below 32 belong on grappa_gemm");
+    GRAPPA_CHECK_ARG(ceil_div(M, 128) <= 65535 && M <= 2147483647LL / 4 && N <= 2147483647LL / 4 && K <= 2147483647LL / 4, "matrix too large");
+    GemmParams p;
+    p.A = A; p.B = nullptr; p.C = C; p.bias = bias; p.res1 = res1; p.res2 = res2;
+    p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = 0; p.ldc = ldc; p.ldr1 = ldr1; p.ldr2 = ldr2;
+    p.act = act; p.drop_p = drop_p; p.drop_scale = 1.0f / (1.0f - drop_p); p.seed = seed; p.seed_dev = seed_dev;
+    p.elu_out = elu_out; p.ld_eo = ld_eo;
+    p.B_hi16 = B_hi; p.B_lo16 = B_lo; p.ldb16 = ldb16;
+    p.cta_budget = (math_mode >> 8) & 0xFF;
+    p.a_vec = 1; p.b_vec = 1;
+    p.c_vec = aligned16(C) && (ldc % 4 == 0);
+    return gemm_bf16_launch(p, (cudaStream_t)stream, workspace, workspace_floats);
+}

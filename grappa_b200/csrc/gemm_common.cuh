@@ -14,6 +14,8 @@ struct GemmParams {
     // ELU'(x) = 1 for x > 0, exp(x) = s + 1 otherwise
     const float* elu_out = nullptr; int64_t ld_eo = 0;
     const float* B_lo = nullptr;   // optional pre-split lo plane of B (same shape / ldb): see gemm_tc.cu B_PRE
+    // bf16x3 path (gemm_tc.cu, gemm_bf16_kernel): B given as pre-split bf16 planes (N, K) with leading dimension ldb16
+    const uint16_t* B_hi16 = nullptr; const uint16_t* B_lo16 = nullptr; int64_t ldb16 = 0;
     int cta_budget = 0;        // > 0: background GEMM (weight gradients on a side stream): split-K grids are sized for this
                                // many CTAs instead of the whole machine, so that the critical chain always finds free SMs
 };
@@ -22,6 +24,8 @@ __device__ __forceinline__ float elu_grad_from_out(float s) { return s > 0.f ? 1
 
 int gemm_tc_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,
                      bool* handled);   // gemm_tc.cu
+
+int gemm_bf16_launch(const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats);   // gemm_tc.cu
 
 // streaming kernels for GEMMs with one dimension <= 8 (gemm_skinny.cu)
 int gemm_skinny_dispatch(int layout, const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats,

@@ -15,6 +15,7 @@
 // (NT / NN / TN) need no transposes.  Out-of-range rows / k are zero-filled by TMA.
 #include "gemm_common.cuh"
 #include <cuda.h>
+#include <cuda_bf16.h>
 
 namespace grappa {
 
@@ -222,6 +223,143 @@ __device__ __forceinline__ void writeout_interior_dispatch(const GemmParams& p, 
     } else {
         if (drop) writeout_interior<NRES, false, true>(p, tile, warp, lane, m0, n0, seed);
         else writeout_interior<NRES, false, false>(p, tile, warp, lane, m0, n0, seed);
+    }
+}
+
+// Write-out of the staged accumulator tile (shared memory, [128][EPI_LD] floats at `smem`) by all ten warps: each warp
+// streams whole rows (512 contiguous bytes per instruction), four rows in flight per iteration.  Split-K slices go to
+// `partial` without an epilogue.
+__device__ __forceinline__ void writeout_tile(const GemmParams& p, uint8_t* smem, int warp, int lane, int m0, int n0,
+                                              float* __restrict__ partial) {
+    const uint32_t tile = smem_u32(smem) + lane * 16;          // this lane's four columns of row 0
+    const int64_t n = (int64_t)n0 + lane * 4;
+    const int nvalid = (int)max((int64_t)0, min((int64_t)4, p.N - n));
+    constexpr int RPI = 4;
+    if (partial != nullptr) {
+        float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
+        const bool vec = (p.N % 4 == 0);
+        if (vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N) {       // interior tile: branch-free
+            float* cp = dst + ((int64_t)m0 + warp * RPI) * p.N + n;
+            uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
+#pragma unroll 1
+            for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
+                float4 a4[RPI];
+#pragma unroll
+                for (int i = 0; i < RPI; ++i) a4[i] = lds128(ts + i * (EPI_LD * 4));
+#pragma unroll
+                for (int i = 0; i < RPI; ++i) *reinterpret_cast<float4*>(cp + i * p.N) = a4[i];
+                ts += (THREADS / 32) * RPI * (EPI_LD * 4);
+                cp += (THREADS / 32) * RPI * p.N;
+            }
+        } else
+        for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
+#pragma unroll
+            for (int i = 0; i < RPI; ++i) {
+                const int r = r0 + i;
+                const int64_t m = (int64_t)m0 + r;
+                if (r >= BM || m >= p.M || nvalid == 0) continue;
+                const float4 a4 = lds128(tile + r * (EPI_LD * 4));
+                float* cp = dst + m * p.N + n;
+                if (vec && nvalid == 4) {
+                    *reinterpret_cast<float4*>(cp) = a4;
+                } else {
+                    if (nvalid > 0) cp[0] = a4.x;
+                    if (nvalid > 1) cp[1] = a4.y;
+                    if (nvalid > 2) cp[2] = a4.z;
+                    if (nvalid > 3) cp[3] = a4.w;
+                }
+            }
+        }
+    } else {
+        const bool has_drop = p.drop_p > 0.f;
+        const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
+        const bool al1 = !p.res1 || ((p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0));
+        const bool al2 = !p.res2 || ((p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0));
+        const bool alb = !p.bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
+        const bool interior = p.c_vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N;
+        if (interior && p.elu_out && !p.bias && !p.res1 && !p.res2 && p.act == 0 && !has_drop && (p.ld_eo % 4 == 0) &&
+            ((reinterpret_cast<uintptr_t>(p.elu_out) & 15) == 0)) {
+            writeout_interior_actgrad(p, tile, warp, lane, m0, n0);
+        } else if (interior && !p.elu_out && al1 && al2 && alb && !(p.res2 && !p.res1)) {
+            const bool act = p.act == 1;
+            if (p.res2) writeout_interior_dispatch<2>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+            else if (p.res1) writeout_interior_dispatch<1>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+            else writeout_interior_dispatch<0>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
+        } else {
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.bias) {
+            if (nvalid > 0) bv.x = __ldg(p.bias + n);
+            if (nvalid > 1) bv.y = __ldg(p.bias + n + 1);
+            if (nvalid > 2) bv.z = __ldg(p.bias + n + 2);
+            if (nvalid > 3) bv.w = __ldg(p.bias + n + 3);
+        }
+        const bool vec_res1 = p.res1 && nvalid == 4 && (p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0);
+        const bool vec_res2 = p.res2 && nvalid == 4 && (p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0);
+        for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
+            float4 a4[RPI], q1[RPI], q2[RPI];
+            bool ok[RPI];
+#pragma unroll
+            for (int i = 0; i < RPI; ++i) {           // issue all loads of the four rows first
+                const int r = r0 + i;
+                const int64_t m = (int64_t)m0 + r;
+                ok[i] = r < BM && m < p.M && nvalid > 0;
+                a4[i] = q1[i] = q2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!ok[i]) continue;
+                a4[i] = lds128(tile + r * (EPI_LD * 4));
+                if (p.res1) {
+                    const float* rp = p.res1 + m * p.ldr1 + n;
+                    if (vec_res1) q1[i] = __ldg(reinterpret_cast<const float4*>(rp));
+                    else {
+                        q1[i].x = __ldg(rp);
+                        if (nvalid > 1) q1[i].y = __ldg(rp + 1);
+                        if (nvalid > 2) q1[i].z = __ldg(rp + 2);
+                        if (nvalid > 3) q1[i].w = __ldg(rp + 3);
+                    }
+                }
+                if (p.res2) {
+                    const float* rp = p.res2 + m * p.ldr2 + n;
+                    if (vec_res2) q2[i] = __ldg(reinterpret_cast<const float4*>(rp));
+                    else {
+                        q2[i].x = __ldg(rp);
+                        if (nvalid > 1) q2[i].y = __ldg(rp + 1);
+                        if (nvalid > 2) q2[i].z = __ldg(rp + 2);
+                        if (nvalid > 3) q2[i].w = __ldg(rp + 3);
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < RPI; ++i) {
+                if (!ok[i]) continue;
+                const int64_t m = (int64_t)m0 + r0 + i;
+                float v[4] = {a4[i].x + bv.x, a4[i].y + bv.y, a4[i].z + bv.z, a4[i].w + bv.w};
+                if (p.act == 1) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) v[j] = elu1(v[j]);
+                }
+                if (has_drop) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        v[j] = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? v[j] * p.drop_scale : 0.f;
+                }
+                v[0] = (v[0] + q1[i].x) + q2[i].x; v[1] = (v[1] + q1[i].y) + q2[i].y; v[2] = (v[2] + q1[i].z) + q2[i].z; v[3] = (v[3] + q1[i].w) + q2[i].w;
+                if (p.elu_out) {
+                    const float* ep = p.elu_out + m * p.ld_eo + n;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (j < nvalid) v[j] *= elu_grad_from_out(__ldg(ep + j));
+                }
+                float* cp = p.C + m * p.ldc + n;
+                if (p.c_vec && nvalid == 4) {
+                    *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+                } else {
+                    if (nvalid > 0) cp[0] = v[0];
+                    if (nvalid > 1) cp[1] = v[1];
+                    if (nvalid > 2) cp[2] = v[2];
+                    if (nvalid > 3) cp[3] = v[3];
+                }
+            }
+        }
+        }   // general (edge / unaligned) path
     }
 }
 
@@ -446,138 +584,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // each warp streams whole rows (512 contiguous bytes per instruction), four rows in flight per iteration.
     __syncthreads();
     STAMP(6, threadIdx.x == 192);
-    {
-        const uint32_t tile = smem_u32(smem) + lane * 16;          // this lane's four columns of row 0
-        const int64_t n = (int64_t)n0 + lane * 4;
-        const int nvalid = (int)max((int64_t)0, min((int64_t)4, p.N - n));
-        constexpr int RPI = 4;
-        if (partial != nullptr) {
-            float* dst = partial + (int64_t)blockIdx.z * p.M * p.N;
-            const bool vec = (p.N % 4 == 0);
-            if (vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N) {       // interior tile: branch-free
-                float* cp = dst + ((int64_t)m0 + warp * RPI) * p.N + n;
-                uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
-#pragma unroll 1
-                for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
-                    float4 a4[RPI];
-#pragma unroll
-                    for (int i = 0; i < RPI; ++i) a4[i] = lds128(ts + i * (EPI_LD * 4));
-#pragma unroll
-                    for (int i = 0; i < RPI; ++i) *reinterpret_cast<float4*>(cp + i * p.N) = a4[i];
-                    ts += (THREADS / 32) * RPI * (EPI_LD * 4);
-                    cp += (THREADS / 32) * RPI * p.N;
-                }
-            } else
-            for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
-#pragma unroll
-                for (int i = 0; i < RPI; ++i) {
-                    const int r = r0 + i;
-                    const int64_t m = (int64_t)m0 + r;
-                    if (r >= BM || m >= p.M || nvalid == 0) continue;
-                    const float4 a4 = lds128(tile + r * (EPI_LD * 4));
-                    float* cp = dst + m * p.N + n;
-                    if (vec && nvalid == 4) {
-                        *reinterpret_cast<float4*>(cp) = a4;
-                    } else {
-                        if (nvalid > 0) cp[0] = a4.x;
-                        if (nvalid > 1) cp[1] = a4.y;
-                        if (nvalid > 2) cp[2] = a4.z;
-                        if (nvalid > 3) cp[3] = a4.w;
-                    }
-                }
-            }
-        } else {
-            const bool has_drop = p.drop_p > 0.f;
-            const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
-            const bool al1 = !p.res1 || ((p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0));
-            const bool al2 = !p.res2 || ((p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0));
-            const bool alb = !p.bias || ((reinterpret_cast<uintptr_t>(p.bias) & 15) == 0);
-            const bool interior = p.c_vec && (int64_t)m0 + BM <= p.M && (int64_t)n0 + BN <= p.N;
-            if (interior && p.elu_out && !p.bias && !p.res1 && !p.res2 && p.act == 0 && !has_drop && (p.ld_eo % 4 == 0) &&
-                ((reinterpret_cast<uintptr_t>(p.elu_out) & 15) == 0)) {
-                writeout_interior_actgrad(p, tile, warp, lane, m0, n0);
-            } else if (interior && !p.elu_out && al1 && al2 && alb && !(p.res2 && !p.res1)) {
-                const bool act = p.act == 1;
-                if (p.res2) writeout_interior_dispatch<2>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
-                else if (p.res1) writeout_interior_dispatch<1>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
-                else writeout_interior_dispatch<0>(p, tile, warp, lane, m0, n0, seed, act, has_drop);
-            } else {
-            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (p.bias) {
-                if (nvalid > 0) bv.x = __ldg(p.bias + n);
-                if (nvalid > 1) bv.y = __ldg(p.bias + n + 1);
-                if (nvalid > 2) bv.z = __ldg(p.bias + n + 2);
-                if (nvalid > 3) bv.w = __ldg(p.bias + n + 3);
-            }
-            const bool vec_res1 = p.res1 && nvalid == 4 && (p.ldr1 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res1) & 15) == 0);
-            const bool vec_res2 = p.res2 && nvalid == 4 && (p.ldr2 % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.res2) & 15) == 0);
-            for (int r0 = warp * RPI; r0 < BM; r0 += (THREADS / 32) * RPI) {
-                float4 a4[RPI], q1[RPI], q2[RPI];
-                bool ok[RPI];
-#pragma unroll
-                for (int i = 0; i < RPI; ++i) {           // issue all loads of the four rows first
-                    const int r = r0 + i;
-                    const int64_t m = (int64_t)m0 + r;
-                    ok[i] = r < BM && m < p.M && nvalid > 0;
-                    a4[i] = q1[i] = q2[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (!ok[i]) continue;
-                    a4[i] = lds128(tile + r * (EPI_LD * 4));
-                    if (p.res1) {
-                        const float* rp = p.res1 + m * p.ldr1 + n;
-                        if (vec_res1) q1[i] = __ldg(reinterpret_cast<const float4*>(rp));
-                        else {
-                            q1[i].x = __ldg(rp);
-                            if (nvalid > 1) q1[i].y = __ldg(rp + 1);
-                            if (nvalid > 2) q1[i].z = __ldg(rp + 2);
-                            if (nvalid > 3) q1[i].w = __ldg(rp + 3);
-                        }
-                    }
-                    if (p.res2) {
-                        const float* rp = p.res2 + m * p.ldr2 + n;
-                        if (vec_res2) q2[i] = __ldg(reinterpret_cast<const float4*>(rp));
-                        else {
-                            q2[i].x = __ldg(rp);
-                            if (nvalid > 1) q2[i].y = __ldg(rp + 1);
-                            if (nvalid > 2) q2[i].z = __ldg(rp + 2);
-                            if (nvalid > 3) q2[i].w = __ldg(rp + 3);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < RPI; ++i) {
-                    if (!ok[i]) continue;
-                    const int64_t m = (int64_t)m0 + r0 + i;
-                    float v[4] = {a4[i].x + bv.x, a4[i].y + bv.y, a4[i].z + bv.z, a4[i].w + bv.w};
-                    if (p.act == 1) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) v[j] = elu1(v[j]);
-                    }
-                    if (has_drop) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            v[j] = hash_uniform(seed, (uint64_t)(m * p.N + n + j)) >= p.drop_p ? v[j] * p.drop_scale : 0.f;
-                    }
-                    v[0] = (v[0] + q1[i].x) + q2[i].x; v[1] = (v[1] + q1[i].y) + q2[i].y; v[2] = (v[2] + q1[i].z) + q2[i].z; v[3] = (v[3] + q1[i].w) + q2[i].w;
-                    if (p.elu_out) {
-                        const float* ep = p.elu_out + m * p.ld_eo + n;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (j < nvalid) v[j] *= elu_grad_from_out(__ldg(ep + j));
-                    }
-                    float* cp = p.C + m * p.ldc + n;
-                    if (p.c_vec && nvalid == 4) {
-                        *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
-                    } else {
-                        if (nvalid > 0) cp[0] = v[0];
-                        if (nvalid > 1) cp[1] = v[1];
-                        if (nvalid > 2) cp[2] = v[2];
-                        if (nvalid > 3) cp[3] = v[3];
-                    }
-                }
-            }
-            }   // general (edge / unaligned) path
-        }
-    }
+    writeout_tile(p, smem, warp, lane, m0, n0, partial);
     STAMP(7, threadIdx.x == 192);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -611,6 +618,199 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmParams p, int sp
         if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n);
         if (p.elu_out) z *= elu_grad_from_out(__ldg(p.elu_out + m * p.ld_eo + n));
         p.C[m * p.ldc + n] = z;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ bf16x3 ----------
+// Same product structure as above with BF16 operand planes:  A B ~ A_hi B_hi + A_hi B_lo + A_lo B_hi,
+// hi = rn_bf16(x), lo = rn_bf16(x - hi)  (16 mantissa bits per operand; the dropped terms are ~2^-17 relative per
+// product: measured through the whole parameter path in profiles/r02_split_precision.md).  kind::f16 MMAs run at twice the
+// tf32 rate and the planes are half the bytes, which is what binds the mainloop (shared-memory bandwidth).
+//   - B is a WEIGHT matrix whose planes were made once per optimiser step (grappa_split_bf16) in the layout this GEMM
+//     wants (K-major: rows = output features of this GEMM, contraction contiguous), so TMA loads them as they are;
+//   - A (activations, fp32, K-major) is TMA-loaded raw and split by the split warps into two bf16 tiles written in the
+//     canonical SWIZZLE_128B K-major layout (128-byte rows = 64 k, 16-byte chunk index XOR row % 8).
+// BK = 32: stage = A_raw 16 KB + A_hi, A_lo, B_hi, B_lo 8 KB each (64-byte rows, SWIZZLE_64B) = 48 KB, FOUR stages: what
+// bounds this kernel is the latency of the TMA -> split -> MMA chain of a stage (~1 us), which only a deep ring hides
+// (measured: two 96 KB stages of BK = 64 ran 1.13 us per 64 k; A through global loads + registers 1.4 us).
+// Shared-memory traffic per 32-wide k-block: 32 KB TMA + 16 KB split reads + 16 KB plane stores + 40 KB operand reads
+// = 104 KB (3xTF32 path: 160 KB), and the tensor pipe needs half the time.
+namespace b16 {
+constexpr int BK = 32, STAGES = 4, KB_PER_CHUNK = 4;
+constexpr int RAW_BYTES = BM * BK * 4, PLANE_BYTES = BM * BK * 2;
+constexpr int STAGE_BYTES = RAW_BYTES + 4 * PLANE_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// two fp32 -> packed bf16x2 (round to nearest even); `lo16` lands in the low half
+__device__ __forceinline__ uint32_t pack_bf16(float lo16, float hi16) {
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi16), "f"(lo16));
+    return r;
+}
+
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapBhi,
+                 const __grid_constant__ CUtensorMap mapBlo, GemmParams p, int kb_per_split, float* __restrict__ partial) {
+    constexpr int BK = b16::BK, STAGES = b16::STAGES, KB_PER_CHUNK = b16::KB_PER_CHUNK;     // (shadow the tf32 kernel's)
+    constexpr int RAW_BYTES = b16::RAW_BYTES, PLANE_BYTES = b16::PLANE_BYTES, STAGE_BYTES = b16::STAGE_BYTES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+    uint64_t* full = bars;                       // TMA landed                    (count 1 + tx bytes)
+    uint64_t* split = bars + STAGES;             // A planes are ready            (count 128)
+    uint64_t* empty = bars + 2 * STAGES;         // MMAs of the stage done        (count 1, via tcgen05.commit)
+    uint64_t* chunk_full = bars + 3 * STAGES;    // [2] slice accumulator complete (count 1, via tcgen05.commit)
+    uint64_t* chunk_empty = bars + 3 * STAGES + 2;   // [2] slice accumulator drained (count 128)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int nk_total = (int)((p.K + BK - 1) / BK);
+    const int kb_begin = blockIdx.z * kb_per_split;
+    const int nk = min(kb_per_split, nk_total - kb_begin);
+    const int n_chunks = (nk + KB_PER_CHUNK - 1) / KB_PER_CHUNK;
+
+    auto issue_loads = [&](int kb) {
+        const int s = kb % STAGES;
+        uint8_t* st = smem + s * STAGE_BYTES;
+        mbar_expect_tx(&full[s], RAW_BYTES + 2 * PLANE_BYTES);
+        const int k0 = (kb_begin + kb) * BK;
+        tma_load_2d(st, &mapA, &full[s], k0, m0);                                      // raw fp32 (SWIZZLE_128B)
+        tma_load_2d(st + RAW_BYTES + 2 * PLANE_BYTES, &mapBhi, &full[s], k0, n0);      // bf16 planes (SWIZZLE_64B)
+        tma_load_2d(st + RAW_BYTES + 3 * PLANE_BYTES, &mapBlo, &full[s], k0, n0);
+    };
+
+    if (threadIdx.x == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapBhi)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&mapBlo)) : "memory");
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&split[s], 128); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&chunk_full[b], 1); mbar_init(&chunk_empty[b], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (int kb = 0; kb < min(nk, STAGES); ++kb) issue_loads(kb);
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = min(nk, STAGES); kb < nk; ++kb) {
+                mbar_wait(&empty[kb % STAGES], ((kb / STAGES) - 1) & 1);
+                issue_loads(kb);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // instruction descriptor (kind::f16): D = F32 (1 << 4), A = B = BF16 (1 << 7, 1 << 10), both K-major
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            const uint32_t idesc2 = (idesc & ~(0x3Fu << 17)) | ((uint32_t)((2 * BN) >> 3) << 17);
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % STAGES;
+                const int chunk = kb / KB_PER_CHUNK, buf = chunk & 1;
+                const bool chunk_start = (kb % KB_PER_CHUNK) == 0;
+                if (chunk_start && chunk >= 2) {
+                    mbar_wait(&chunk_empty[buf], ((chunk >> 1) - 1) & 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                mbar_wait(&split[s], (kb / STAGES) & 1);                  // A planes written (which implies: TMA landed)
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t a_hi = smem_u32(smem + s * STAGE_BYTES) + RAW_BYTES, a_lo = a_hi + PLANE_BYTES;
+                const uint32_t b_hi = a_hi + 2 * PLANE_BYTES;            // B_lo follows B_hi: one N = 256 MMA covers both
+                const uint32_t tmem_buf = tmem_base + buf * (2 * BN);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                    // 16 bf16 = 32 bytes per MMA inside the 64-byte swizzle row; 8-row groups 512 B apart; layout 4 = SWIZZLE_64B
+                    const uint32_t off = k * 32;
+                    const uint64_t dah = make_desc(a_hi + off, 16, 512, 4), dal = make_desc(a_lo + off, 16, 512, 4);
+                    const uint64_t dbh = make_desc(b_hi + off, 16, 512, 4);
+                    umma_bf16(tmem_buf, dah, dbh, idesc2, !(chunk_start && k == 0));
+                    umma_bf16(tmem_buf + BN, dal, dbh, idesc, 1);
+                }
+                umma_commit(&empty[s]);
+                if ((kb % KB_PER_CHUNK) == KB_PER_CHUNK - 1 || kb == nk - 1) umma_commit(&chunk_full[buf]);
+            }
+        }
+    } else if (warp < 6) {
+        // split workers: thread = tile row; raw row = 8 swizzled 16-byte chunks (SWIZZLE_128B: chunk ^ row % 8), output rows
+        // = 4 chunks of 8 bf16 per plane (SWIZZLE_64B: chunk ^ (row / 2) % 4)
+        const int r = threadIdx.x - 64;
+        const uint32_t sw128 = (uint32_t)(r & 7), sw64 = (uint32_t)((r >> 1) & 3);
+        for (int kb = 0; kb < nk; ++kb) {
+            const int s = kb % STAGES;
+            mbar_wait(&full[s], (kb / STAGES) & 1);
+            const uint32_t raw = smem_u32(smem + s * STAGE_BYTES) + r * 128;
+            const uint32_t hi = smem_u32(smem + s * STAGE_BYTES) + RAW_BYTES + r * 64, lo = hi + PLANE_BYTES;
+            float4 x[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) x[c] = lds128(raw + (((uint32_t)c ^ sw128) << 4));      // all loads in flight first
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float v[8] = {x[2 * j].x, x[2 * j].y, x[2 * j].z, x[2 * j].w, x[2 * j + 1].x, x[2 * j + 1].y, x[2 * j + 1].z, x[2 * j + 1].w};
+                uint32_t h[4], l[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    h[q] = pack_bf16(v[2 * q], v[2 * q + 1]);
+                    const float f0 = __uint_as_float(h[q] << 16), f1 = __uint_as_float(h[q] & 0xFFFF0000u);
+                    l[q] = pack_bf16(v[2 * q] - f0, v[2 * q + 1] - f1);
+                }
+                const uint32_t dst = ((uint32_t)j ^ sw64) << 4;
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(hi + dst), "r"(h[0]), "r"(h[1]), "r"(h[2]), "r"(h[3]) : "memory");
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(lo + dst), "r"(l[0]), "r"(l[1]), "r"(l[2]), "r"(l[3]) : "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(&split[s]);
+        }
+    } else {
+        // accumulate + epilogue staging (warps 6..9): as in gemm_tc_kernel
+        const int q = warp & 3;
+        const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
+        float acc[BN];
+#pragma unroll
+        for (int j = 0; j < BN; ++j) acc[j] = 0.f;
+        for (int c = 0; c < n_chunks; ++c) {
+            const int buf = c & 1;
+            mbar_wait(&chunk_full[buf], (c >> 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int cb = 0; cb < BN / 16; ++cb) {
+                uint32_t rr[16], xx[16];
+                tmem_ld16(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + cb * 16), rr);
+                tmem_ld16(tmem_base + lane_addr + (uint32_t)(buf * 2 * BN + BN + cb * 16), xx);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 16; ++j) acc[cb * 16 + j] += __uint_as_float(rr[j]) + __uint_as_float(xx[j]);
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&chunk_empty[buf]);
+        }
+        const uint32_t row = smem_u32(smem) + (q * 32 + lane) * EPI_LD * 4;
+#pragma unroll
+        for (int j4 = 0; j4 < BN / 4; ++j4)
+            sts128(row + j4 * 16, make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]));
+    }
+    __syncthreads();
+    writeout_tile(p, smem, warp, lane, m0, n0, partial);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
     }
 }
 
@@ -685,6 +885,55 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
     return 0;
 }
 
+// 2-D bf16 tensor map over a row-major (rows x cols, leading dimension ld elements) plane, box 32 cols x 128 rows
+static bool make_map_bf16(CUtensorMap* map, const uint16_t* base, int64_t rows, int64_t cols, int64_t ld) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)b16::BK, (cuuint32_t)BN};           // 32 bf16 = 64-byte rows
+    cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<uint16_t*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static int launch_bf16(const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats) {
+    CUtensorMap ma, mbh, mbl;
+    if (!make_map(&ma, p.A, p.M, p.K, p.lda, 32, BM, false) || !make_map_bf16(&mbh, p.B_hi16, p.N, p.K, p.ldb16) ||
+        !make_map_bf16(&mbl, p.B_lo16, p.N, p.K, p.ldb16))
+        return fail("grappa_gemm_bf16x3: %s cuTensorMapEncodeTiled failed (operands must be 16-byte aligned, ld * size %% 16 == 0)", "");
+    static std::atomic<bool> configured[64];
+    int dev = 0;
+    GRAPPA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev].load(std::memory_order_acquire)) {
+        GRAPPA_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, b16::SMEM_BYTES));
+        if (dev >= 0 && dev < 64) configured[dev].store(true, std::memory_order_release);
+    }
+    const int64_t tiles = ceil_div(p.N, BN) * ceil_div(p.M, BM);
+    const int nk = (int)ceil_div(p.K, b16::BK);
+    int splits = 1;
+    const int64_t budget = p.cta_budget > 0 ? p.cta_budget : 148;
+    if (workspace != nullptr && tiles <= budget / 2 && nk >= 32) {          // same policy as the tf32 path
+        const int want = (int)std::min<int64_t>(budget / tiles, nk / 16);
+        if (want > 1 && (int64_t)want * p.M * p.N <= workspace_floats) splits = want;
+    }
+    int kps = nk;
+    if (splits > 1) {
+        kps = (int)ceil_div(ceil_div(nk, splits), b16::KB_PER_CHUNK) * b16::KB_PER_CHUNK;
+        splits = (int)ceil_div(nk, kps);
+    }
+    dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM), (unsigned)splits);
+    gemm_bf16_kernel<<<grid, THREADS, b16::SMEM_BYTES, st>>>(ma, mbh, mbl, p, kps, splits > 1 ? workspace : nullptr);
+    GRAPPA_CHECK_LAUNCH();
+    if (splits > 1) {
+        const int64_t total = p.M * p.N;
+        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8), 256, 0, st>>>(p, splits, workspace);
+        GRAPPA_CHECK_LAUNCH();
+    }
+    return 0;
+}
+
 }  // namespace tc
 
 // lo plane of a pre-split operand, exactly what the split warps compute: lo = rn_tf32(x - trunc19(x))
@@ -697,6 +946,50 @@ __global__ void __launch_bounds__(256) split_lo_kernel(int64_t n4, const float4*
         l.z = tc::tf32_rn(v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u));
         l.w = tc::tf32_rn(v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u));
         lo[i] = l;
+    }
+}
+
+int gemm_bf16_launch(const GemmParams& p, cudaStream_t st, float* workspace, int64_t workspace_floats) {
+    return tc::launch_bf16(p, st, workspace, workspace_floats);
+}
+
+// bf16 hi / lo planes of a batch of weight matrices, in both orientations (see grappa_split_bf16): one CTA per 32 x 32
+// tile of one matrix, transposed through shared memory.
+__global__ void __launch_bounds__(256) split_bf16_kernel(int n_mats, const int64_t* __restrict__ table, const float* __restrict__ params,
+                                                         uint16_t* __restrict__ planes) {
+    const int64_t* t = table + (int64_t)blockIdx.y * 4;
+    const int64_t src = t[0], rows = t[1], cols = t[2], dst = t[3];
+    const int64_t tiles_c = (cols + 31) / 32, tiles_r = (rows + 31) / 32;
+    if ((int64_t)blockIdx.x >= tiles_c * tiles_r) return;
+    const int64_t tr = blockIdx.x / tiles_c, tcn = blockIdx.x % tiles_c;
+    const int64_t ldk = (cols + 7) / 8 * 8, ldn = (rows + 7) / 8 * 8;
+    uint16_t* hi = planes + dst;
+    uint16_t* lo = hi + rows * ldk;
+    uint16_t* hiT = lo + rows * ldk;
+    uint16_t* loT = hiT + cols * ldn;
+    __shared__ uint32_t tile[32][33];          // packed (hi | lo << 16)
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int i = ty; i < 32; i += 8) {
+        const int64_t r = tr * 32 + i, c = tcn * 32 + tx;
+        uint32_t v = 0;
+        if (r < rows && c < cols) {
+            const float x = params[src + r * cols + c];
+            const __nv_bfloat16 h = __float2bfloat16_rn(x);
+            const __nv_bfloat16 l = __float2bfloat16_rn(x - __bfloat162float(h));
+            v = (uint32_t)__bfloat16_as_ushort(h) | ((uint32_t)__bfloat16_as_ushort(l) << 16);
+            hi[r * ldk + c] = (uint16_t)(v & 0xffff);
+            lo[r * ldk + c] = (uint16_t)(v >> 16);
+        }
+        tile[i][tx] = v;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int64_t c = tcn * 32 + i, r = tr * 32 + tx;      // transposed: row = original column
+        if (c < cols && r < rows) {
+            const uint32_t v = tile[tx][i];
+            hiT[c * ldn + r] = (uint16_t)(v & 0xffff);
+            loT[c * ldn + r] = (uint16_t)(v >> 16);
+        }
     }
 }
 
@@ -752,6 +1045,23 @@ extern "C" int grappa_split_lo(int64_t n, const float* x, float* lo, void* strea
     const int64_t n4 = n / 4;
     grappa::split_lo_kernel<<<(unsigned)std::min<int64_t>(grappa::ceil_div(n4, 256), 148 * 16), 256, 0, (cudaStream_t)stream>>>(
         n4, reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(lo));
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+
+/* see include/grappa_b200.h */
+extern "C" int64_t grappa_split_bf16_elems(int64_t rows, int64_t cols) {
+    const int64_t ldk = (cols + 7) / 8 * 8, ldn = (rows + 7) / 8 * 8;
+    return (2 * rows * ldk + 2 * cols * ldn + 7) / 8 * 8;
+}
+
+extern "C" int grappa_split_bf16(int64_t n_mats, const int64_t* table, int64_t max_tiles, const float* params, uint16_t* planes,
+                                 void* stream) {
+    GRAPPA_CHECK_ARG(n_mats >= 0 && n_mats <= 65535 && max_tiles >= 0 && max_tiles < 2147483647LL, "bad sizes");
+    if (n_mats == 0 || max_tiles == 0) return 0;
+    GRAPPA_CHECK_ARG(table && params && planes, "null pointer");
+    grappa::split_bf16_kernel<<<dim3((unsigned)max_tiles, (unsigned)n_mats), 256, 0, (cudaStream_t)stream>>>((int)n_mats, table, params, planes);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }

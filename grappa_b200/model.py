@@ -374,7 +374,10 @@ class Symmetriser(nn.Module):
         for perm in self._perms_host:                   # x_perm block i = x block perm[i]  ->  column block j takes block i with perm[i] = j
             inv = [perm.index(j) for j in range(self.n_seq)]
             wp = wv[:, inv, :].reshape(H, D).contiguous()
-            views.append((wp, ops.split_lo(wp) if ops.USE_WEIGHT_LO and ops.MATH_MODE == 1 else None))
+            if ops.MATH_MODE == 2:
+                views.append((wp, ops.make_planes(wp)))
+            else:
+                views.append((wp, ops.split_lo(wp) if ops.USE_WEIGHT_LO and ops.MATH_MODE == 1 else None))
         bias = torch.addmv(b1, w1, b).contiguous()
         ones, zeros = torch.ones_like(g), torch.zeros_like(g)
         out = (views, bias, ones, zeros)
@@ -388,7 +391,11 @@ class Symmetriser(nn.Module):
         xh = ops.layer_norm(x.view(T, D), ones, zeros)                      # x_hat: statistics once per tuple
         z = torch.empty((len(views) * T, H), device=x.device, dtype=torch.float32)
         for p_i, (wp, lo) in enumerate(views):                              # rows [p T, (p+1) T) = permutation p
-            ops.gemm(0, T, H, D, xh, D, wp, D, z[p_i * T:(p_i + 1) * T], H, bias=bias, act=ops.ACT_ELU, b_lo=lo)
+            if isinstance(lo, ops.WeightPlanes) and T >= 32:
+                ops.gemm_bf16(T, H, D, xh, D, lo.nt, z[p_i * T:(p_i + 1) * T], H, bias=bias, act=ops.ACT_ELU)
+            else:
+                ops.gemm(0, T, H, D, xh, D, wp, D, z[p_i * T:(p_i + 1) * T], H, bias=bias, act=ops.ACT_ELU,
+                         b_lo=None if isinstance(lo, ops.WeightPlanes) else lo)
         rows = ops.linear(z, ff.linear2.weight, ff.linear2.bias)
         for layer in list(self.mlp)[1:]:
             rows = layer(rows)

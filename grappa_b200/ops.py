@@ -13,7 +13,9 @@ import torch
 from . import _lib
 
 import os as _os
-MATH_MODE = int(_os.environ.get("GRAPPA_MATH_MODE", "1"))   # 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm)
+# 0 = fp32 FFMA GEMM tiles, 1 = tcgen05 3xTF32 tiles (see grappa_gemm), 2 = tcgen05 bf16x3 tiles for the GEMMs whose B
+# operand is a weight (forward and dX; grappa_gemm_bf16x3) and 3xTF32 for the rest (weight gradients)
+MATH_MODE = int(_os.environ.get("GRAPPA_MATH_MODE", "2"))
 ACT_NONE, ACT_ELU = 0, 1
 # Optional {id(parameter): gradient buffer}: backward kernels write parameter gradients straight into these buffers
 # (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
@@ -177,7 +179,7 @@ def _gemm_mode():
     budget = SIDE_CTA_BUDGET if _IN_SIDE[0] else 0
     if not budget and WRITER_CTA_BUDGET and torch.cuda.current_stream().cuda_stream in THROUGHPUT_STREAMS:
         budget = WRITER_CTA_BUDGET
-    return MATH_MODE | (budget << 8) | (0x10000 if _IN_SIDE[0] else 0)     # bit 16: bookkeeping only (ignored by the library)
+    return min(MATH_MODE, 1) | (budget << 8) | (0x10000 if _IN_SIDE[0] else 0)     # bit 16: bookkeeping only (ignored by the library)
 
 
 def gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
@@ -212,7 +214,7 @@ def split_lo(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tenso
 
 def weight_lo(w: torch.Tensor):
     """lo plane of a weight matrix for the B operand of the NT / NN GEMMs, or None."""
-    if not USE_WEIGHT_LO or MATH_MODE != 1 or w.dim() != 2 or w.shape[1] % 4 or w.shape[1] < 32 or w.shape[0] < 32 or not w.is_contiguous():
+    if not USE_WEIGHT_LO or MATH_MODE < 1 or w.dim() != 2 or w.shape[1] % 4 or w.shape[1] < 32 or w.shape[0] < 32 or not w.is_contiguous():
         return None
     if WEIGHT_LO is not None:
         return WEIGHT_LO.get(id(w))
@@ -225,6 +227,64 @@ def weight_lo(w: torch.Tensor):
     lo = split_lo(w.detach())
     _LO_CACHE[key] = (weakref.ref(w, lambda _r, k=key: _LO_CACHE.pop(k, None)), stamp, lo)
     return lo
+
+
+class WeightPlanes:
+    """bf16 hi / lo planes of one weight matrix W (N, K) in both orientations (grappa_split_bf16): `nt` = planes of W for
+    y = x W^T, `nn` = planes of W^T for dx = dy W; each (hi pointer, lo pointer, leading dimension)."""
+    __slots__ = ("buf", "nt", "nn", "shape")
+
+    def __init__(self, buf: torch.Tensor, base_elems: int, N: int, K: int):
+        ldk, ldn = (K + 7) // 8 * 8, (N + 7) // 8 * 8
+        p0 = buf.data_ptr() + 2 * base_elems
+        self.buf, self.shape = buf, (N, K)
+        self.nt = (p0, p0 + 2 * N * ldk, ldk)
+        self.nn = (p0 + 4 * N * ldk, p0 + 4 * N * ldk + 2 * K * ldn, ldn)
+
+
+WEIGHT_PLANES = None      # {id(parameter): WeightPlanes}, set by the training-step driver (refreshed after every AdamW)
+_PLANE_CACHE = {}
+
+
+def make_planes(w: torch.Tensor) -> WeightPlanes:
+    """Planes of one (N, K) fp32 matrix, made now (one launch)."""
+    w = _req(w, "weight").contiguous()
+    N, K = w.shape
+    L = _lib.lib()
+    buf = torch.zeros(int(L.grappa_split_bf16_elems(N, K)), dtype=torch.int16, device=w.device)
+    table = torch.tensor([0, N, K, 0], dtype=torch.int64, device=w.device)
+    _lib.check(L.grappa_split_bf16(1, _p(table), ((N + 31) // 32) * ((K + 31) // 32), _p(w), _p(buf), _stream()))
+    return WeightPlanes(buf, 0, N, K)
+
+
+def weight_planes(w: torch.Tensor):
+    """bf16 planes of a weight matrix for grappa_gemm_bf16x3, or None (mode off / shape not eligible)."""
+    if MATH_MODE != 2 or w.dim() != 2 or w.shape[0] < 32 or w.shape[1] < 32 or not w.is_contiguous():
+        return None
+    if WEIGHT_PLANES is not None:
+        return WEIGHT_PLANES.get(id(w))
+    key = id(w)
+    hit = _PLANE_CACHE.get(key)
+    stamp = (w._version, w.data_ptr(), WEIGHT_EPOCH[0])
+    if hit is not None and hit[0]() is w and hit[1] == stamp:
+        return hit[2]
+    pl = make_planes(w.detach())
+    _PLANE_CACHE[key] = (weakref.ref(w, lambda _r, k=key: _PLANE_CACHE.pop(k, None)), stamp, pl)
+    return pl
+
+
+def _bf16_ok(A: torch.Tensor, lda: int, M: int, N: int, K: int) -> bool:
+    return M >= 32 and N >= 32 and K >= 32 and lda % 4 == 0 and A.data_ptr() % 16 == 0
+
+
+def gemm_bf16(M, N, K, A, lda, planes3, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
+              drop_p=0.0, seed=0, seed_dev=None, elu_out=None, ld_eo=0):
+    """C[M,N] = epi(A[M,K] . Bw[N,K]^T) with Bw given as bf16 planes (hi pointer, lo pointer, ld)."""
+    ws = _workspace(C.device)
+    wsf = WORKSPACE_FLOATS if ws is not None else 0
+    _lib.check(_lib.lib().grappa_gemm_bf16x3(M, N, K, _p(A), lda, planes3[0], planes3[1], planes3[2], _p(C), ldc, _p(bias), act,
+                                             _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), _gemm_mode(),
+                                             _p(ws), wsf, _p(elu_out), ld_eo, _stream()))
 
 
 def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo, b_lo=None):
@@ -260,9 +320,15 @@ class LinearFn(torch.autograd.Function):
             r2, l2 = _rows2d(res2, "res2")
         seed = DropoutSeeds.next() if drop_p > 0 else 0
         seed_dev = DropoutSeeds.dev if drop_p > 0 else None
-        w_lo = weight_lo(weight) if ldb == K else None
-        gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev, b_lo=w_lo)
+        planes = weight_planes(weight) if ldb == K else None
+        w_lo = None
+        if planes is not None and _bf16_ok(x, lda, M, N, K):
+            gemm_bf16(M, N, K, x, lda, planes.nt, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev)
+        else:
+            w_lo = weight_lo(weight) if ldb == K else None
+            gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev, b_lo=w_lo)
         ctx.w_lo = w_lo
+        ctx.planes = planes
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
                               r2 if act != ACT_NONE else None)
         if grad_is_preact and (act != ACT_ELU or drop_p > 0 or res1 is not None or res2 is not None):
@@ -323,7 +389,9 @@ class LinearFn(torch.autograd.Function):
             param_grads()
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
-            if x_is_elu_out:
+            if ctx.planes is not None and _bf16_ok(dz, lddz, M, K, N):     # dx = dz W: the planes of W^T are K-major for it
+                gemm_bf16(M, K, N, dz, lddz, ctx.planes.nn, dx, K, elu_out=x if x_is_elu_out else None, ld_eo=lda if x_is_elu_out else 0)
+            elif x_is_elu_out:
                 gemm_actgrad(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, x, lda, b_lo=ctx.w_lo)
             else:
                 gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, b_lo=ctx.w_lo)

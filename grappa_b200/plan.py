@@ -151,6 +151,8 @@ def build_plan(g, block_atoms: int = ENERGY_BLOCK_ATOMS, n_parts: Optional[int] 
         if energy and "xyz" in g.nodes["n1"].data:
             ctas = p.n_mol * ((int(g.nodes["n1"].data["xyz"].shape[1]) + 31) // 32)
             n_parts = ENERGY_PARTS if ctas >= 600 else (8 if ctas >= 150 else 16)
+            if len(bnn) and int(bnn.max()) > block_atoms:
+                n_parts = ENERGY_PARTS      # molecules spanning blocks use un-compacted accumulators (parts x block atoms rows)
 
     keep = []
     idx_ptrs = (ctypes.c_void_p * 4)()

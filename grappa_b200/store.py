@@ -65,9 +65,14 @@ class CollatedSpec:
 
 class MoleculeStore:
     def __init__(self, molecules: Sequence[HeteroGraph], device, feature_names: Optional[List[str]] = None,
-                 energy_parts: int = 16):
+                 energy_parts: Optional[int] = None):
         """`energy_parts`: warps per CTA of the energy kernel for batches collated from this store (every molecule's
-        plan is compiled for it; training batches have few CTAs, hence many short parts: plan.build_plan)."""
+        plan is compiled for it).  Default: 16 (training batches have few CTAs, hence many short parts: plan.build_plan),
+        4 when a molecule spans several atom blocks (un-compacted accumulators: parts x block atoms rows of shared memory)."""
+        if energy_parts is None:
+            from .plan import ENERGY_BLOCK_ATOMS, ENERGY_PARTS
+            energy_parts = ENERGY_PARTS if max(int(g.num_nodes("n1")) for g in molecules) > ENERGY_BLOCK_ATOMS else 16
+        self.energy_parts = int(energy_parts)
         if len(molecules) == 0:
             raise ValueError("empty molecule store")
         self.device = torch.device(device)

@@ -100,6 +100,12 @@ class TrainStep:
         if ops.USE_WEIGHT_LO:                                   # lo planes of the initial weights (refreshed after every AdamW)
             _lib.check(_lib.lib().grappa_split_lo(self.flat.numel, ops._p(self.flat.params), ops._p(self.flat.params_lo),
                                                   ops._stream()))
+        # bf16 planes of every weight matrix for the bf16x3 GEMMs (ops.MATH_MODE 2): one flat buffer, refreshed by ONE launch
+        # after every AdamW (grappa_split_bf16 over a device-resident table of the matrices in the updated range)
+        self._plane_tables = {}
+        self._planes = None
+        if ops.MATH_MODE == 2:
+            self._init_planes()
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         self.weights = (energy_weight, gradient_weight, proper_regularisation, improper_regularisation)
         self.world_size = world_size
@@ -159,7 +165,9 @@ class TrainStep:
     # ---- one forward + loss + backward on device-resident inputs -------------------------------------------------
     def _fwd_bwd(self, g):
         ops.GRAD_SINK = self.flat.sink
-        ops.WEIGHT_LO = self.flat.lo_of if ops.USE_WEIGHT_LO else None
+        # (bf16 mode: the flat tf32 lo planes are not maintained; the rare fallback GEMM makes its lo plane on demand)
+        ops.WEIGHT_LO = self.flat.lo_of if (ops.USE_WEIGHT_LO and self._planes is None) else None
+        ops.WEIGHT_PLANES = self.flat.planes_of if self._planes is not None else None
         ops.DropoutSeeds.dev = self.seed_dev
         try:
             plan = get_plan(g)
@@ -201,6 +209,7 @@ class TrainStep:
         finally:
             ops.GRAD_SINK = None
             ops.WEIGHT_LO = None
+            ops.WEIGHT_PLANES = None
             ops.DropoutSeeds.dev = None
         return loss.detach()
 
@@ -320,6 +329,30 @@ class TrainStep:
         if self.split_update:
             self._writers_ready.record(torch.cuda.current_stream(self.device))
 
+    def _init_planes(self):
+        L = _lib.lib()
+        self._plane_rows = []                       # (param offset, rows, cols, plane offset)
+        total = 0
+        for n, p in self.flat.named:
+            if p.dim() == 2 and p.shape[0] >= 32 and p.shape[1] >= 32:
+                self._plane_rows.append((self.flat.offsets[n], int(p.shape[0]), int(p.shape[1]), total, p))
+                total += int(L.grappa_split_bf16_elems(int(p.shape[0]), int(p.shape[1])))
+        self._planes = torch.zeros(max(total, 8), dtype=torch.int16, device=self.device)
+        self.flat.planes_of = {id(p): ops.WeightPlanes(self._planes, base, r, c) for (_, r, c, base, p) in self._plane_rows}
+        self._refresh_planes(0, self.flat.numel)
+
+    def _refresh_planes(self, lo: int, hi: int):
+        key = (lo, hi)
+        tab = self._plane_tables.get(key)
+        if tab is None:
+            rows = [(o, r, c, b) for (o, r, c, b, _) in self._plane_rows if lo <= o < hi]
+            mt = max([((r + 31) // 32) * ((c + 31) // 32) for (_, r, c, _) in rows], default=0)
+            tab = (torch.tensor(rows, dtype=torch.int64, device=self.device).reshape(-1) if rows else None, len(rows), mt)
+            self._plane_tables[key] = tab
+        if tab[1]:
+            _lib.check(_lib.lib().grappa_split_bf16(tab[1], ops._p(tab[0]), tab[2], ops._p(self.flat.params), ops._p(self._planes),
+                                                    ops._stream()))
+
     def restart_warmup(self):
         self._warmup_step = 0 if self.warmup_steps > 0 else None
 
@@ -343,7 +376,9 @@ class TrainStep:
                                            self._lr_now, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
                                            getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
         ops.WEIGHT_EPOCH[0] += 1         # invalidates lo planes cached for use outside this driver
-        if ops.USE_WEIGHT_LO:            # lo planes of the updated weights for the next step's GEMMs (B operand pre-split)
+        if self._planes is not None:     # bf16 planes of the updated weights for the next step's forward / dX GEMMs
+            self._refresh_planes(lo, hi)
+        elif ops.USE_WEIGHT_LO:          # tf32 lo planes of the updated weights (B operand pre-split, 3xTF32 path)
             _lib.check(_lib.lib().grappa_split_lo(hi - lo, ptr(f.params), ptr(f.params_lo), ops._stream()))
 
     def exchange_and_update(self):

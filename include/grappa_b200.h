@@ -55,6 +55,27 @@ int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
                 float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
                 float* workspace, int64_t workspace_floats, void* stream);
 
+/* Dense layer with BF16 operand planes on tcgen05 kind::f16:  C[M,N] = epi( A[M,K] . Bw[N,K]^T ) with
+ * A B ~ A_hi B_hi + A_hi B_lo + A_lo B_hi, hi = rn_bf16(x), lo = rn_bf16(x - hi) (16 mantissa bits per operand, fp32
+ * accumulation; end-to-end error of the bonded parameters 3e-6 .. 3e-5 relative, profiles/r02_split_precision.md).  Same
+ * call sites as grappa_gemm, for the layers whose B operand is a WEIGHT: B_hi / B_lo are its (N, K) bf16 planes, leading
+ * dimension ldb16, made once per optimiser step by grappa_split_bf16 (the forward uses the planes of W, the dX GEMM the
+ * planes of W^T, so both read K-major planes); A is fp32 and is split inside the kernel.  Epilogue, math_mode bits 8..15
+ * (CTA budget) and workspace as grappa_gemm; elu_out / ld_eo as grappa_gemm_actgrad (may be NULL). */
+int grappa_gemm_bf16x3(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda,
+                       const uint16_t* B_hi, const uint16_t* B_lo, int64_t ldb16, float* C, int64_t ldc,
+                       const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
+                       float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
+                       float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo, void* stream);
+
+/* bf16 planes of a batch of weight matrices in one launch.  table (device, int64 x 4 per matrix): {offset of the matrix
+ * in `params` (floats), rows, cols, offset of its planes in `planes` (uint16 elements)}; per matrix the planes are
+ * [hi (rows, ldk) | lo (rows, ldk) | hi^T (cols, ldn) | lo^T (cols, ldn)] with ldk = cols and ldn = rows rounded up to 8
+ * (pad columns are never read: the GEMM's tensor maps end at K); grappa_split_bf16_elems gives that size.
+ * max_tiles = max over matrices of ceil(rows / 32) * ceil(cols / 32). */
+int64_t grappa_split_bf16_elems(int64_t rows, int64_t cols);
+int grappa_split_bf16(int64_t n_mats, const int64_t* table, int64_t max_tiles, const float* params, uint16_t* planes, void* stream);
+
 /* Backward GEMM with the activation derivative fused into its epilogue: C = (A op B) * ELU'(pre-activation), the
  * derivative read off the saved ELU OUTPUT s (ELU'(x) = 1 for x > 0, else exp(x) = s + 1).  Used for dL/d(pre) of the
  * first layer of every Linear-ELU-Linear block (network_utils.py:44-54, graph_attention.py:304-317), where autograd in

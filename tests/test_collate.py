@@ -38,9 +38,11 @@ def apply_float_segments(seg, conf, store, out):
         out[dst:dst + rows * cd * inner] = block[:, sel, :].reshape(-1)
 
 
-def host_reference(mols, ids, conf_idxs):
+def host_reference(mols, ids, conf_idxs, n_parts):
+    from grappa_b200.plan import build_plan
     C = conf_idxs.shape[1]
-    return PackedBatch(batch([set_number_confs(mols[i], C, conf_idxs=conf_idxs[j]) for j, i in enumerate(ids)]), pin=False)
+    g = batch([set_number_confs(mols[i], C, conf_idxs=conf_idxs[j]) for j, i in enumerate(ids)])
+    return PackedBatch(g, pin=False, plan=build_plan(g, n_parts=n_parts))      # same energy parts as the store's molecules
 
 
 def make_molecules():
@@ -69,7 +71,7 @@ def test_segment_tables_reproduce_host_collate(ids, C):
     gen = torch.Generator().manual_seed(3)
     conf = torch.stack([conf_indices(int(mols[i].nodes["n1"].data["xyz"].shape[1]), C, gen) for i in ids])
     spec = store.prepare(ids, conf_idxs=conf)
-    ref = host_reference(mols, ids, conf)
+    ref = host_reference(mols, ids, conf, store.energy_parts)
     ibuf = np.full(spec.n_int, -77, np.int32)
     fbuf = np.full(spec.n_float, np.nan, np.float32)
     seg = spec.seg64.numpy()
@@ -124,7 +126,7 @@ def test_device_collate_bit_exact_and_trainable():
     for ids, C in (([0, 1, 2], 4), ([2, 2, 0, 3], 6), ([4, 0], 7), ([len(mols) - 1, 0, 4], 5)):
         gen = torch.Generator().manual_seed(5)
         conf = torch.stack([conf_indices(int(mols[i].nodes["n1"].data["xyz"].shape[1]), C, gen) for i in ids])
-        ref = host_reference(mols, ids, conf)
+        ref = host_reference(mols, ids, conf, store.energy_parts)
         db = store.collate(ids, conf_idxs=conf)
         torch.cuda.synchronize()
         spec = store.prepare(ids, conf_idxs=conf)
@@ -137,7 +139,7 @@ def test_device_collate_bit_exact_and_trainable():
             if spec2.signature == spec.signature:
                 store.collate_into(spec2, db)
                 torch.cuda.synchronize()
-                check_sections(spec2, db.ibuf.cpu().numpy(), db.fbuf.cpu().numpy(), host_reference(mols, ids2, conf2))
+                check_sections(spec2, db.ibuf.cpu().numpy(), db.fbuf.cpu().numpy(), host_reference(mols, ids2, conf2, store.energy_parts))
 
 
 @pytest.mark.gpu

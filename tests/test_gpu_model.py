@@ -504,8 +504,11 @@ def test_folded_symmetriser_matches_the_explicit_permutations(monkeypatch):
                 monkeypatch.setattr(M, "FOLD_SYMMETRISER", True)
             with torch.no_grad():
                 outs.append(graph_params(model(g_host.to(DEV))))
+        # two evaluation orders of the same function: the bar is the rounding noise of the GEMM math mode in use
+        # (3xTF32: 2e-5; bf16x3: 16 mantissa bits per operand, 4x that), far inside the 1e-4 parity budget either way
+        tol = 2e-5 if ops.MATH_MODE < 2 else 8e-5
         for lvl in LEVELS:
             for key, v in outs[0][lvl].items():
                 scale = float(v.abs().max()) + 1e-12
-                assert float((v - outs[1][lvl][key]).abs().max()) / scale < 2e-5, f"{lvl} {key}"
-                assert float((ref2[lvl][key] - outs[2][lvl][key]).abs().max()) / (float(ref2[lvl][key].abs().max()) + 1e-12) < 2e-5
+                assert float((v - outs[1][lvl][key]).abs().max()) / scale < tol, f"{lvl} {key}"
+                assert float((ref2[lvl][key] - outs[2][lvl][key]).abs().max()) / (float(ref2[lvl][key].abs().max()) + 1e-12) < tol
