@@ -291,6 +291,9 @@ def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo, b_lo=N
     gemm(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out=elu_out, ld_eo=ld_eo, b_lo=b_lo)
 
 
+_SKIP_DW = _os.environ.get("GRAPPA_SKIP_DW", "0") == "1"      # timing experiments only: wrong gradients
+
+
 class LinearFn(torch.autograd.Function):
     """y = dropout(act(x W^T + b)) + res1 + res2, columns padded to `out_ld` (pad columns are zero).
 
@@ -376,7 +379,8 @@ class LinearFn(torch.autograd.Function):
             nonlocal dw
             if ctx.needs_input_grad[1]:
                 dw = w_tgt if w_tgt is not None else torch.empty((N, K), device=dy.device, dtype=torch.float32)
-                gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
+                if not _SKIP_DW:
+                    gemm(2, N, K, M, dz, lddz, x, lda, dw, K)
                 if w_tgt is not None:
                     dw = None
             if want_db and not db_done:
