@@ -189,6 +189,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="eager launches instead of CUDA-graph replay")
     ap.add_argument("--no-split-update", action="store_true",
                     help="one all-reduce + one AdamW after backward instead of the GNN / writers split (A/B switch)")
+    ap.add_argument("--split-update", action="store_true", help="staged update under the next forward also on one GPU (A/B switch)")
     ap.add_argument("--math-mode", type=int, default=None)
     args = ap.parse_args()
     if args.impl == "reference":
@@ -216,7 +217,7 @@ def main():
     model = GrappaModel.from_default_config()
     sd_cpu = {k: v.clone() for k, v in model.state_dict().items()}
     ts = TrainStep(model, dev, lr=1e-5, weight_decay=0.0, world_size=world, use_cuda_graph=not args.no_graph,
-                   split_update=False if args.no_split_update else None)
+                   split_update=False if args.no_split_update else (True if args.split_update else None))
     ops.DropoutSeeds.manual_seed(1234 + rank)  # dropout streams differ per rank
     g_host = build_batch(first_seed=MOLS_PER_RANK * rank)
     packed = PackedBatch(g_host, pin=True)

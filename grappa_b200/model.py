@@ -198,8 +198,11 @@ class GrappaGNN(nn.Module):
         lin = self.pre_dense[0]
         p0 = self.initial_dropout.p if self.training else 0.0
         h = ops.linear(x, lin.weight, lin.bias, act=ops.ACT_ELU, drop_p=p0)
+        hook = getattr(self, "stage_hook", None)     # training driver: called before block i >= 1 reads its parameters
         if not self.no_convs:
-            for block in self.blocks:
+            for i, block in enumerate(self.blocks):
+                if hook is not None and i >= 1:
+                    hook(i)
                 h = block(plan, h)
         lin = self.post_dense[0]
         pf = self.final_dropout.p if self.training else 0.0

@@ -136,6 +136,7 @@ class TrainStep:
         self._upd_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._writers_ready = torch.cuda.Event(external=True)
         self._writers_ready.record(torch.cuda.current_stream(self.device))
+        self._stage_ready = []          # filled below once the stage boundaries are known
         self._loss_host = [torch.zeros(1).pin_memory() if torch.cuda.is_available() else torch.zeros(1) for _ in range(4)]
         self._loss_slot = 0
         self._works = []
@@ -152,6 +153,29 @@ class TrainStep:
         first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
         self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
         assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
+        # Staged update (world_size > 1): the parameters are exchanged + updated in FORWARD order in five stages --
+        # [pre_dense + GNN block 0 | block 1 | block 2 | block 3 + post_dense | the four writers].  Stage 0 runs on the compute
+        # stream; stages 1..4 (all-reduce wait + AdamW + plane refresh) on the update stream UNDER the next step's forward,
+        # which waits for stage i only right before it reads that stage's parameters (external-event wait nodes in the
+        # step graph).  Exposed communication = the first stage's all-reduce (1/8 of the gradient bytes).
+        bounds = [0]
+        n_blocks = len(getattr(self.model.gnn, "blocks", []))
+        for i in range(1, n_blocks):
+            first = [self.flat.offsets[n] for n, _ in self.flat.named if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}.")]
+            if first:
+                bounds.append(min(first))
+        bounds += [self.bucket_split, self.flat.numel]
+        self._stage_bounds = sorted(set(bounds))
+        self._stage_of_block = {}
+        for i in range(1, n_blocks):
+            first = [self.flat.offsets[n] for n, _ in self.flat.named if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}.")]
+            if first:
+                self._stage_of_block[i] = self._stage_bounds.index(min(first))
+        self._writer_stage = self._stage_bounds.index(self.bucket_split) if self.bucket_split in self._stage_bounds[:-1] else None
+        for _ in range(len(self._stage_bounds) - 1):
+            ev = torch.cuda.Event(external=True)
+            ev.record(torch.cuda.current_stream(self.device))
+            self._stage_ready.append(ev)
         self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.device)
         # static device buffers + captured graph per batch SHAPE (signature), least recently used first.  Real datasets
         # have many shapes: only `max_cached_shapes` stay resident (each holds its activations' memory pool).
@@ -171,9 +195,13 @@ class TrainStep:
         ops.DropoutSeeds.dev = self.seed_dev
         try:
             plan = get_plan(g)
-            for lvl, (lo, hi) in self._writer_ranges.items():
-                if lvl not in g.ntypes or plan.T[lvl] == 0:
-                    self.flat.grads[lo:hi].zero_()          # (a memset node of the captured step)
+
+            def clear_skipped_writers():
+                for lvl, (lo, hi) in self._writer_ranges.items():
+                    if lvl not in g.ntypes or plan.T[lvl] == 0:
+                        self.flat.grads[lo:hi].zero_()          # (a memset node of the captured step)
+            if not self.split_update:
+                clear_skipped_writers()
             if self.overlap_comm:
                 plan = get_plan(g)
                 g = self.model.gnn(g, plan)
@@ -181,8 +209,15 @@ class TrainStep:
                 g = self.energy(self.model.parameter_writer(g, plan))
             elif self.split_update:
                 plan = get_plan(g)
-                g = self.model.gnn(g, plan)
-                self._writers_ready.wait(torch.cuda.current_stream(self.device))     # writers' parameters of the last update
+                cur = torch.cuda.current_stream(self.device)
+                self.model.gnn.stage_hook = lambda i: self._stage_ready[self._stage_of_block[i]].wait(cur) if i in self._stage_of_block else None
+                try:
+                    g = self.model.gnn(g, plan)
+                finally:
+                    self.model.gnn.stage_hook = None
+                if self._writer_stage is not None:
+                    self._stage_ready[self._writer_stage].wait(cur)                  # writers' parameters of the last update
+                clear_skipped_writers()      # only now: the deferred AdamW of the last step has finished reading the gradients
                 g = self.energy(self.model.parameter_writer(g, plan))
             else:
                 g = self.energy(self.model(g))
@@ -327,7 +362,8 @@ class TrainStep:
         self._lr_now = self._next_lr()
         self._adamw_range(0, self.flat.numel)
         if self.split_update:
-            self._writers_ready.record(torch.cuda.current_stream(self.device))
+            for ev in self._stage_ready:
+                ev.record(torch.cuda.current_stream(self.device))
 
     def _init_planes(self):
         L = _lib.lib()
@@ -390,23 +426,25 @@ class TrainStep:
             return
         dist = torch.distributed
         cur = torch.cuda.current_stream(self.device)
-        n, sp = self.flat.numel, self.bucket_split
-        w1 = w2 = None
+        b = self._stage_bounds
+        works = [None] * (len(b) - 1)
         if self.world_size > 1:
-            w1 = dist.all_reduce(self.flat.grads[:sp], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
-            w2 = dist.all_reduce(self.flat.grads[sp:], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+            for i in range(len(b) - 1):                            # issued in forward order: NCCL completes them in that order
+                works[i] = dist.all_reduce(self.flat.grads[b[i]:b[i + 1]], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         self._grad_scale = 1.0 / self.world_size
         self.t += 1
         self._lr_now = self._next_lr()
         self._upd_stream.wait_stream(cur)                       # gradients of this step are complete
-        if w1 is not None:
-            w1.wait()
-        self._adamw_range(0, sp)
+        if works[0] is not None:
+            works[0].wait()
+        self._adamw_range(b[0], b[1])
+        self._stage_ready[0].record(cur)
         with torch.cuda.stream(self._upd_stream):
-            if w2 is not None:
-                w2.wait()
-            self._adamw_range(sp, n)
-            self._writers_ready.record(self._upd_stream)
+            for i in range(1, len(b) - 1):
+                if works[i] is not None:
+                    works[i].wait()
+                self._adamw_range(b[i], b[i + 1])
+                self._stage_ready[i].record(self._upd_stream)
 
     def synchronize(self):
         """All parameter updates issued so far have completed on the device."""
