@@ -432,6 +432,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int b = 0; b < 2; ++b) { mbar_init(&chunk_full[b], 1); mbar_init(&chunk_empty[b], 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         // the ring is empty: fill it right away, in the shadow of the TMEM allocation and the CTA-wide barrier below
+        pdl_wait();                              // (first access to memory written by the preceding kernels)
         for (int kb = 0; kb < min(nk, STAGES); ++kb) issue_loads(kb);
     }
     if (warp == 1) {
@@ -441,6 +442,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    pdl_wait();
     STAMP(1, threadIdx.x == 0);
     const uint32_t tmem_base = *tmem_slot;       // two ping-pong slice accumulators of 256 columns: [hi*hi | cross terms]
 
@@ -584,6 +586,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // each warp streams whole rows (512 contiguous bytes per instruction), four rows in flight per iteration.
     __syncthreads();
     STAMP(6, threadIdx.x == 192);
+    pdl_trigger();      // mainloop done: the next kernel of the stream may start its prologue under this write-out
     writeout_tile(p, smem, warp, lane, m0, n0, partial);
     STAMP(7, threadIdx.x == 192);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -598,6 +601,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 // split-K reduction: C = epilogue( sum_z partial[z] ), fixed summation order (deterministic).  The slices are L2-resident
 // and the loop over them is latency-bound, so loads are issued four slices at a time before they are added in order.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmParams p, int splits, const float* __restrict__ partial) {
+    pdl_trigger();
+    pdl_wait();
     const int64_t total = p.M * p.N;
     const bool has_drop = p.drop_p > 0.f;
     const uint64_t seed = has_drop ? p.seed + (p.seed_dev ? *p.seed_dev : 0ull) : 0ull;
@@ -697,6 +702,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&split[s], 128); mbar_init(&empty[s], 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&chunk_full[b], 1); mbar_init(&chunk_empty[b], 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pdl_wait();
         for (int kb = 0; kb < min(nk, STAGES); ++kb) issue_loads(kb);
     }
     if (warp == 1) {
@@ -706,6 +712,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    pdl_wait();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
@@ -805,6 +812,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             sts128(row + j4 * 16, make_float4(acc[j4 * 4], acc[j4 * 4 + 1], acc[j4 * 4 + 2], acc[j4 * 4 + 3]));
     }
     __syncthreads();
+    pdl_trigger();      // mainloop done: the next kernel of the stream may start its prologue under this write-out
     writeout_tile(p, smem, warp, lane, m0, n0, partial);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -875,11 +883,13 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMa
         splits = (int)ceil_div(nk, kps);
     }
     dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM), (unsigned)splits);
-    gemm_tc_kernel<A_MN, B_MN, B_PRE><<<grid, THREADS, SMEM_BYTES, st>>>(ma, mb, mblo, p, kps, splits > 1 ? workspace : nullptr);
+    GRAPPA_CUDA(launch_pdl(gemm_tc_kernel<A_MN, B_MN, B_PRE>, grid, dim3(THREADS), SMEM_BYTES, st, ma, mb, mblo, p, kps,
+                           splits > 1 ? workspace : (float*)nullptr));
     GRAPPA_CHECK_LAUNCH();
     if (splits > 1) {
         const int64_t total = p.M * p.N;
-        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8), 256, 0, st>>>(p, splits, workspace);
+        GRAPPA_CUDA(launch_pdl(splitk_reduce_kernel, dim3((unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8)), dim3(256), 0, st,
+                               p, splits, (const float*)workspace));
         GRAPPA_CHECK_LAUNCH();
     }
     return 0;
@@ -924,11 +934,13 @@ static int launch_bf16(const GemmParams& p, cudaStream_t st, float* workspace, i
         splits = (int)ceil_div(nk, kps);
     }
     dim3 grid((unsigned)ceil_div(p.N, BN), (unsigned)ceil_div(p.M, BM), (unsigned)splits);
-    gemm_bf16_kernel<<<grid, THREADS, b16::SMEM_BYTES, st>>>(ma, mbh, mbl, p, kps, splits > 1 ? workspace : nullptr);
+    GRAPPA_CUDA(launch_pdl(gemm_bf16_kernel, grid, dim3(THREADS), b16::SMEM_BYTES, st, ma, mbh, mbl, p, kps,
+                           splits > 1 ? workspace : (float*)nullptr));
     GRAPPA_CHECK_LAUNCH();
     if (splits > 1) {
         const int64_t total = p.M * p.N;
-        splitk_reduce_kernel<<<(unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8), 256, 0, st>>>(p, splits, workspace);
+        GRAPPA_CUDA(launch_pdl(splitk_reduce_kernel, dim3((unsigned)std::min<int64_t>(ceil_div(total, 256), 148 * 8)), dim3(256), 0, st,
+                               p, splits, (const float*)workspace));
         GRAPPA_CHECK_LAUNCH();
     }
     return 0;
