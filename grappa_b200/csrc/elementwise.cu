@@ -414,10 +414,10 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
                                     const float* gamma, const float* mean, const float* rstd,
                                     float* dX, int64_t lddx, float* dgamma, float* dbeta, float* scratch, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && D > 0, "bad sizes");
-    GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && dX, "null pointer");
+    GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && (dX || dgamma), "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     const bool vec = D % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0 && al16(X) && al16(dY) && al16(dX) && al16(gamma);
-    if (M > 0) {
+    if (M > 0 && dX != nullptr) {          // dX == NULL: only the affine reductions (issued on a side stream by the caller)
         const unsigned grid = (unsigned)ceil_div(M * 32, 256);
         if (vec) layernorm_bwd_dx_kernel<true><<<grid, 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
         else layernorm_bwd_dx_kernel<false><<<grid, 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);

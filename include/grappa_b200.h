@@ -137,6 +137,7 @@ int grappa_colsum_noalloc(int64_t M, int64_t N, const float* X, int64_t ldx, flo
  * network_utils.py:46,115,129, perm_equiv_transformer.py:80.  mean/rstd: (M) saved for backward. */
 int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_t ldx, const float* gamma, const float* beta,
                          float* Y, int64_t ldy, float* mean, float* rstd, void* stream);
+/* dX may be NULL (only dgamma / dbeta: their column reductions on a side stream) or dgamma / dbeta / scratch NULL (only dX). */
 int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D);
 int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64_t lddy, const float* X, int64_t ldx,
                          const float* gamma, const float* mean, const float* rstd,
