@@ -23,7 +23,7 @@ PROTOTYPES = {
     "grappa_gemm_actgrad": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I64, I, P, I64, P]),
     "grappa_gemm_ex": (I, [I, I64, I64, I64, P, I64, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P, P]),
     "grappa_split_lo": (I, [I64, P, P, P]),
-    "grappa_gemm_bf16x3": (I, [I64, I64, I64, P, I64, P, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P]),
+    "grappa_gemm_bf16x3": (I, [I64, I64, I64, P, I64, P, P, I64, P, I64, P, I, P, I64, P, I64, F, c_uint64, P, I, P, I64, P, I64, P, P]),
     "grappa_split_bf16_elems": (I64, [I64, I64]),
     "grappa_split_bf16": (I, [I64, P, I64, P, P, P]),
     "grappa_epilogue_bwd": (I, [I64, I64, P, I64, P, I64, P, I64, P, I64, I, F, c_uint64, P, P, I64, P, P, P]),
@@ -38,9 +38,9 @@ PROTOTYPES = {
     "grappa_gnn_attn_bwd": (I, [I64, I, I, P, P, P, P, P, P, P, P, P, P, P]),
     "grappa_tuple_gather_fwd": (I, [I64, I, I, I, P, I64, P, P, P, P]),
     "grappa_tuple_gather_bwd": (I, [I64, I, I, P, P, P, P, I64, P]),
-    "grappa_tuple_attn_fwd": (I, [I64, I, I, I, P, P, P]),
-    "grappa_tuple_attn_bwd": (I, [I64, I, I, I, P, P, P, P]),
-    "grappa_token_residual": (I, [I64, I, I, P, P, P, P]),
+    "grappa_tuple_attn_fwd": (I, [I64, I, I, I, P, P, P, P]),
+    "grappa_tuple_attn_bwd": (I, [I64, I, I, I, P, P, P, P, P]),
+    "grappa_token_residual": (I, [I64, I, I, P, P, P, P, P]),
     "grappa_token_residual_bwd": (I, [I64, I, I, P, P, P]),
     "grappa_symm_permute_fwd": (I, [I64, I, I, I, P, P, P, P]),
     "grappa_symm_permute_bwd": (I, [I64, I, I, I, P, P, P, P]),

@@ -350,11 +350,12 @@ __global__ void featurize_kernel(int64_t n_atoms, FeatBlocks fb, const float* __
 // ------------------------------------------------------------------------------------- token residual ---------
 
 __global__ void token_residual_kernel(int64_t M, int W, int F, const float* __restrict__ X3, const float* __restrict__ X,
-                                      float* __restrict__ R) {
+                                      const int32_t* __restrict__ row_idx, float* __restrict__ R) {
     const int64_t total = M * W;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int c = (int)(i % W);
-        const float x = X[i];
+        // row_idx: token -> row of the table of distinct token contents (the gather of the transformer input is fused in)
+        const float x = row_idx ? X[(int64_t)__ldg(row_idx + i / W) * W + c] : X[i];
         R[i] = X3[i] + (c < F ? x + x : x);
     }
 }
@@ -592,10 +593,11 @@ extern "C" int grappa_featurize(int64_t n_atoms, int n_blocks, const float* cons
     return 0;
 }
 
-extern "C" int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, float* R, void* stream) {
+extern "C" int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, const int32_t* row_idx, float* R,
+                                     void* stream) {
     if (M == 0) return 0;
     GRAPPA_CHECK_ARG(X3 && X && R && W > 0, "bad arguments");
-    token_residual_kernel<<<grid_for(M * W), 256, 0, (cudaStream_t)stream>>>(M, W, F, X3, X, R);
+    token_residual_kernel<<<grid_for(M * W), 256, 0, (cudaStream_t)stream>>>(M, W, F, X3, X, row_idx, R);
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }

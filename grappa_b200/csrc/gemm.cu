@@ -293,8 +293,10 @@ extern "C" int grappa_gemm_bf16x3(int64_t M, int64_t N, int64_t K, const float* 
                                   const uint16_t* B_hi, const uint16_t* B_lo, int64_t ldb16, float* C, int64_t ldc,
                                   const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
                                   float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
-                                  float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo, void* stream) {
+                                  float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo,
+                                  const int32_t* res1_idx, void* stream) {
     GRAPPA_CHECK_ARG(M >= 0 && N >= 0 && K >= 0, "negative size");
+    GRAPPA_CHECK_ARG(res1_idx == nullptr || res1 != nullptr, "res1_idx without res1");
     GRAPPA_CHECK_ARG(act == 0 || act == 1, "act must be 0 (none) or 1 (ELU)");
     GRAPPA_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "drop_p must be in [0,1)");
     GRAPPA_CHECK_ARG(elu_out == nullptr || ld_eo >= N, "ld_eo must be >= N");
@@ -309,7 +311,7 @@ extern "C" int grappa_gemm_bf16x3(int64_t M, int64_t N, int64_t K, const float* 
     p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = 0; p.ldc = ldc; p.ldr1 = ldr1; p.ldr2 = ldr2;
     p.act = act; p.drop_p = drop_p; p.drop_scale = 1.0f / (1.0f - drop_p); p.seed = seed; p.seed_dev = seed_dev;
     p.elu_out = elu_out; p.ld_eo = ld_eo;
-    p.B_hi16 = B_hi; p.B_lo16 = B_lo; p.ldb16 = ldb16;
+    p.B_hi16 = B_hi; p.B_lo16 = B_lo; p.ldb16 = ldb16; p.res1_idx = res1_idx;
     p.cta_budget = (math_mode >> 8) & 0xFF;
     p.a_vec = 1; p.b_vec = 1;
     p.c_vec = aligned16(C) && (ldc % 4 == 0);

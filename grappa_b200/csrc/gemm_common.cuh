@@ -16,6 +16,9 @@ struct GemmParams {
     const float* B_lo = nullptr;   // optional pre-split lo plane of B (same shape / ldb): see gemm_tc.cu B_PRE
     // bf16x3 path (gemm_tc.cu, gemm_bf16_kernel): B given as pre-split bf16 planes (N, K) with leading dimension ldb16
     const uint16_t* B_hi16 = nullptr; const uint16_t* B_lo16 = nullptr; int64_t ldb16 = 0;
+    // optional row gather of res1 (tensor-core paths): row m of the residual is res1[res1_idx[m], :] -- the residual is a
+    // table of distinct token contents and is never materialised per token (readout: out_proj + gathered LN(x) rows)
+    const int32_t* res1_idx = nullptr;
     int cta_budget = 0;        // > 0: background GEMM (weight gradients on a side stream): split-K grids are sized for this
                                // many CTAs instead of the whole machine, so that the critical chain always finds free SMs
 };

@@ -152,7 +152,8 @@ __device__ __forceinline__ void writeout_interior(const GemmParams& p, uint32_t 
     if (p.bias) bv = __ldg(reinterpret_cast<const float4*>(p.bias + n));
     const int64_t mrow = (int64_t)m0 + warp * RPI;
     float* cp = p.C + mrow * p.ldc + n;
-    const float* r1 = NRES >= 1 ? p.res1 + mrow * p.ldr1 + n : nullptr;
+    const float* r1 = NRES >= 1 ? p.res1 + (p.res1_idx ? 0 : mrow * p.ldr1) + n : nullptr;
+    const int32_t* ri = (NRES >= 1 && p.res1_idx) ? p.res1_idx + mrow : nullptr;      // gathered residual rows
     const float* r2 = NRES >= 2 ? p.res2 + mrow * p.ldr2 + n : nullptr;
     uint32_t ts = tile + warp * RPI * (EPI_LD * 4);
 #pragma unroll 1
@@ -161,7 +162,7 @@ __device__ __forceinline__ void writeout_interior(const GemmParams& p, uint32_t 
 #pragma unroll
         for (int i = 0; i < RPI; ++i) {
             a[i] = lds128(ts + i * (EPI_LD * 4));
-            if (NRES >= 1) q1[i] = __ldg(reinterpret_cast<const float4*>(r1 + i * p.ldr1));
+            if (NRES >= 1) q1[i] = __ldg(reinterpret_cast<const float4*>(r1 + (ri ? (int64_t)__ldg(ri + i) : (int64_t)i) * p.ldr1));
             if (NRES >= 2) q2[i] = __ldg(reinterpret_cast<const float4*>(r2 + i * p.ldr2));
         }
 #pragma unroll
@@ -182,7 +183,7 @@ __device__ __forceinline__ void writeout_interior(const GemmParams& p, uint32_t 
         }
         ts += PASS * (EPI_LD * 4);
         cp += PASS * p.ldc;
-        if (NRES >= 1) r1 += PASS * p.ldr1;
+        if (NRES >= 1) { if (ri) ri += PASS; else r1 += PASS * p.ldr1; }
         if (NRES >= 2) r2 += PASS * p.ldr2;
     }
 }
@@ -307,7 +308,7 @@ __device__ __forceinline__ void writeout_tile(const GemmParams& p, uint8_t* smem
                 if (!ok[i]) continue;
                 a4[i] = lds128(tile + r * (EPI_LD * 4));
                 if (p.res1) {
-                    const float* rp = p.res1 + m * p.ldr1 + n;
+                    const float* rp = p.res1 + (p.res1_idx ? (int64_t)__ldg(p.res1_idx + m) : m) * p.ldr1 + n;
                     if (vec_res1) q1[i] = __ldg(reinterpret_cast<const float4*>(rp));
                     else {
                         q1[i].x = __ldg(rp);
@@ -619,7 +620,7 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(GemmParams p, int sp
         if (p.bias) z += __ldg(p.bias + n);
         if (p.act == 1) z = elu1(z);
         if (has_drop) z = hash_uniform(seed, (uint64_t)i) >= p.drop_p ? z * p.drop_scale : 0.f;
-        if (p.res1) z += __ldg(p.res1 + m * p.ldr1 + n);
+        if (p.res1) z += __ldg(p.res1 + (p.res1_idx ? (int64_t)__ldg(p.res1_idx + m) : m) * p.ldr1 + n);
         if (p.res2) z += __ldg(p.res2 + m * p.ldr2 + n);
         if (p.elu_out) z *= elu_grad_from_out(__ldg(p.elu_out + m * p.ld_eo + n));
         p.C[m * p.ldc + n] = z;

@@ -161,7 +161,7 @@ __device__ __forceinline__ void axpy8(float s, const float4 (&x)[2], float4 (&y)
 // One warp handles 4 heads of one tuple.
 template <int S>
 __global__ void __launch_bounds__(128) tuple_attn_fwd_kernel(int64_t T, int n_heads, const float* __restrict__ qkv,
-                                                             float* __restrict__ out) {
+                                                             const int32_t* __restrict__ row_idx, float* __restrict__ out) {
     const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     const int groups = n_heads / 4;
@@ -173,7 +173,9 @@ __global__ void __launch_bounds__(128) tuple_attn_fwd_kernel(int64_t T, int n_he
     float4 q[S][2], k[S][2], v[S][2];
 #pragma unroll
     for (int j = 0; j < S; ++j) {
-        const float4* row = reinterpret_cast<const float4*>(qkv + (t * S + j) * 3 * E + head * 64);
+        // row_idx: token -> row of a table of distinct token contents (the gather of the QKV rows is fused in here)
+        const int64_t src = row_idx ? (int64_t)__ldg(row_idx + t * S + j) : t * S + j;
+        const float4* row = reinterpret_cast<const float4*>(qkv + src * 3 * E + head * 64);
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
             q[j][r] = __ldg(row + sub + 8 * r);
@@ -201,6 +203,7 @@ __global__ void __launch_bounds__(128) tuple_attn_fwd_kernel(int64_t T, int n_he
 
 template <int S>
 __global__ void __launch_bounds__(128) tuple_attn_bwd_kernel(int64_t T, int n_heads, const float* __restrict__ qkv,
+                                                             const int32_t* __restrict__ row_idx,
                                                              const float* __restrict__ dOut, float* __restrict__ dqkv) {
     const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -213,7 +216,8 @@ __global__ void __launch_bounds__(128) tuple_attn_bwd_kernel(int64_t T, int n_he
     float4 q[S][2], k[S][2], v[S][2], g[S][2];
 #pragma unroll
     for (int j = 0; j < S; ++j) {
-        const float4* row = reinterpret_cast<const float4*>(qkv + (t * S + j) * 3 * E + head * 64);
+        const int64_t src = row_idx ? (int64_t)__ldg(row_idx + t * S + j) : t * S + j;
+        const float4* row = reinterpret_cast<const float4*>(qkv + src * 3 * E + head * 64);
         const float4* grow = reinterpret_cast<const float4*>(dOut + (t * S + j) * E + head * 64);
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
@@ -480,7 +484,8 @@ extern "C" int grappa_row_gather_bwd(int64_t table_rows, int D, const float* dX,
     return 0;
 }
 
-extern "C" int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, float* out, void* stream) {
+extern "C" int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const int32_t* row_idx,
+                                     float* out, void* stream) {
     GRAPPA_CHECK_ARG(head_dim == 64 && n_heads % 4 == 0 && n_heads > 0, "tuple attention needs head_dim 64 and n_heads % 4 == 0");
     GRAPPA_CHECK_ARG(n_seq >= 1 && n_seq <= 4 && T >= 0, "n_seq must be 1..4");
     if (T == 0) return 0;
@@ -489,17 +494,17 @@ extern "C" int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head
     const unsigned grid = (unsigned)ceil_div(warps * 32, 128);
     cudaStream_t st = (cudaStream_t)stream;
     switch (n_seq) {
-        case 1: tuple_attn_fwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
-        case 2: tuple_attn_fwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
-        case 3: tuple_attn_fwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
-        default: tuple_attn_fwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, out); break;
+        case 1: tuple_attn_fwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, out); break;
+        case 2: tuple_attn_fwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, out); break;
+        case 3: tuple_attn_fwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, out); break;
+        default: tuple_attn_fwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, out); break;
     }
     GRAPPA_CHECK_LAUNCH();
     return 0;
 }
 
-extern "C" int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const float* dOut,
-                                     float* dqkv, void* stream) {
+extern "C" int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const int32_t* row_idx,
+                                     const float* dOut, float* dqkv, void* stream) {
     GRAPPA_CHECK_ARG(head_dim == 64 && n_heads % 4 == 0 && n_heads > 0, "tuple attention needs head_dim 64 and n_heads % 4 == 0");
     GRAPPA_CHECK_ARG(n_seq >= 1 && n_seq <= 4 && T >= 0, "n_seq must be 1..4");
     if (T == 0) return 0;
@@ -508,10 +513,10 @@ extern "C" int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head
     const unsigned grid = (unsigned)ceil_div(warps * 32, 128);
     cudaStream_t st = (cudaStream_t)stream;
     switch (n_seq) {
-        case 1: tuple_attn_bwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
-        case 2: tuple_attn_bwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
-        case 3: tuple_attn_bwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
-        default: tuple_attn_bwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, dOut, dqkv); break;
+        case 1: tuple_attn_bwd_kernel<1><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, dOut, dqkv); break;
+        case 2: tuple_attn_bwd_kernel<2><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, dOut, dqkv); break;
+        case 3: tuple_attn_bwd_kernel<3><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, dOut, dqkv); break;
+        default: tuple_attn_bwd_kernel<4><<<grid, 128, 0, st>>>(T, n_heads, qkv, row_idx, dOut, dqkv); break;
     }
     GRAPPA_CHECK_LAUNCH();
     return 0;

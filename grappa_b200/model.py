@@ -281,12 +281,15 @@ class DottedAttWithMLP(nn.Module):
         x = ops.layer_norm(x, self.norm1.weight, self.norm1.bias)
         return x, ops.linear(x, self.attn.in_proj_weight, self.attn.in_proj_bias)
 
-    def post(self, x, qkv, T, n_seq, outer_residual=None, outer_feats=0):
+    def post(self, x, qkv, T, n_seq, outer_residual=None, outer_feats=0, qkv_gather=None):
+        """qkv_gather = (plan, names): `x`, `qkv` (and `outer_residual`, when given) are TABLES of distinct token contents
+        (one row per (atom, pe)), gathered inside the attention kernel, the out-projection's epilogue and the residual
+        kernel: between the table and the feed-forward block no gathered token tensor is written."""
         p = self.dropout.p if self.training else 0.0
-        o = ops.tuple_attention(qkv, T, n_seq, self.num_heads)
-        x = ops.linear(o, self.attn.out_proj.weight, self.attn.out_proj.bias, res1=x, drop_p=p)
+        o = ops.tuple_attention(qkv, T, n_seq, self.num_heads, gather=qkv_gather)
+        x = ops.linear(o, self.attn.out_proj.weight, self.attn.out_proj.bias, res1=x, drop_p=p, res1_gather=qkv_gather)
         x = ops.layer_norm(x, self.norm2.weight, self.norm2.bias)
-        res = x if outer_residual is None else ops.token_residual(x, outer_residual, outer_feats)
+        res = x if outer_residual is None else ops.token_residual(x, outer_residual, outer_feats, gather=qkv_gather)
         return self.ff(x, extra_residual=res)
 
 
@@ -438,9 +441,12 @@ class SymmetrisedTransformer(nn.Module):
             table = atom_feats if pe is None else ops.pe_table(atom_feats, self.n_feats, self.trafo_out_feats)
             x1_tab, qkv_tab = gt.transformer[0].pre(table)
             rows = T * n_seq
-            x_in = ops.row_gather(table, plan, names, rows)
-            x = gt.transformer[0].post(ops.row_gather(x1_tab, plan, names, rows), ops.row_gather(qkv_tab, plan, names, rows),
-                                       T, n_seq, outer_residual=x_in if n_blocks == 1 else None, outer_feats=self.n_feats)
+            # with one transformer block (the default) the input residual is read straight off the table inside the
+            # residual kernel; deeper stacks need the gathered input again after the last block
+            x_in = table if n_blocks == 1 else ops.row_gather(table, plan, names, rows)
+            x = gt.transformer[0].post(x1_tab, qkv_tab, T, n_seq,
+                                       outer_residual=x_in if n_blocks == 1 else None, outer_feats=self.n_feats,
+                                       qkv_gather=(plan, names))
             first = 1
         else:
             x_in = ops.tuple_gather(atom_feats, plan, level, n_seq, self.n_feats, self.trafo_out_feats,

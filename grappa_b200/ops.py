@@ -278,13 +278,13 @@ def _bf16_ok(A: torch.Tensor, lda: int, M: int, N: int, K: int) -> bool:
 
 
 def gemm_bf16(M, N, K, A, lda, planes3, C, ldc, bias=None, act=0, res1=None, ldr1=0, res2=None, ldr2=0,
-              drop_p=0.0, seed=0, seed_dev=None, elu_out=None, ld_eo=0):
+              drop_p=0.0, seed=0, seed_dev=None, elu_out=None, ld_eo=0, res1_idx=None):
     """C[M,N] = epi(A[M,K] . Bw[N,K]^T) with Bw given as bf16 planes (hi pointer, lo pointer, ld)."""
     ws = _workspace(C.device)
     wsf = WORKSPACE_FLOATS if ws is not None else 0
     _lib.check(_lib.lib().grappa_gemm_bf16x3(M, N, K, _p(A), lda, planes3[0], planes3[1], planes3[2], _p(C), ldc, _p(bias), act,
                                              _p(res1), ldr1, _p(res2), ldr2, float(drop_p), seed, _p(seed_dev), _gemm_mode(),
-                                             _p(ws), wsf, _p(elu_out), ld_eo, _stream()))
+                                             _p(ws), wsf, _p(elu_out), ld_eo, res1_idx, _stream()))
 
 
 def gemm_actgrad(layout, M, N, K, A, lda, B, ldb, C, ldc, elu_out, ld_eo, b_lo=None):
@@ -304,7 +304,9 @@ class LinearFn(torch.autograd.Function):
                     pre-activation."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out=False, grad_is_preact=False):
+    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out=False, grad_is_preact=False, res1_gather=None):
+        # res1_gather = (plan, names): res1 is a TABLE of distinct token contents; row m of the residual is
+        # res1[idx[m]], gathered inside the GEMM epilogue (its gradient is pull-reduced per table row in backward)
         x, lda = _rows2d(x, "x")
         w, ldb = _rows2d(weight, "weight")
         M, K = x.shape
@@ -325,13 +327,23 @@ class LinearFn(torch.autograd.Function):
         seed_dev = DropoutSeeds.dev if drop_p > 0 else None
         planes = weight_planes(weight) if ldb == K else None
         w_lo = None
-        if planes is not None and _bf16_ok(x, lda, M, N, K):
-            gemm_bf16(M, N, K, x, lda, planes.nt, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev)
+        use_bf16 = planes is not None and _bf16_ok(x, lda, M, N, K)
+        if res1_gather is not None and not use_bf16:        # other GEMM paths take a materialised residual
+            r1 = torch.empty((M, r1.shape[1]), device=x.device, dtype=torch.float32)
+            _lib.check(_lib.lib().grappa_row_gather_fwd(M, r1.shape[1], _p(res1), l1, res1_gather[0].ptr(res1_gather[1][0]), _p(r1),
+                                                        r1.shape[1], _stream()))
+            l1 = r1.shape[1]
+        if use_bf16:
+            gemm_bf16(M, N, K, x, lda, planes.nt, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev,
+                      res1_idx=res1_gather[0].ptr(res1_gather[1][0]) if res1_gather is not None else None)
         else:
             w_lo = weight_lo(weight) if ldb == K else None
             gemm(0, M, N, K, x, lda, w, ldb, y, ldc, bias, act, r1, l1, r2, l2, drop_p, seed, seed_dev, b_lo=w_lo)
         ctx.w_lo = w_lo
         ctx.planes = planes
+        ctx.res1_gather = (res1_gather, res1.shape[0]) if res1_gather is not None else None
+        if res1_gather is not None and act != ACT_NONE:
+            raise ValueError("a gathered residual needs act = none (the epilogue backward would need it per token)")
         ctx.save_for_backward(x, w, y if act != ACT_NONE else None, r1 if act != ACT_NONE else None,
                               r2 if act != ACT_NONE else None)
         if grad_is_preact and (act != ACT_ELU or drop_p > 0 or res1 is not None or res2 is not None):
@@ -402,13 +414,19 @@ class LinearFn(torch.autograd.Function):
         if b_sunk:
             db = None
         dr = dy if ldc == N else dy[:, :N]
-        return (dx, dw, db, dr if (has_r1 and ctx.needs_input_grad[3]) else None,
-                dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None, None, None)
+        dr1 = dr if (has_r1 and ctx.needs_input_grad[3]) else None
+        if dr1 is not None and ctx.res1_gather is not None:        # gradient of the table: fixed-order pull over its CSR
+            (plan, names), R = ctx.res1_gather
+            dr1c = dr1.contiguous()
+            dtab = torch.empty((R, N), device=dy.device, dtype=torch.float32)
+            _lib.check(L.grappa_row_gather_bwd(R, N, _p(dr1c), N, plan.ptr(names[1]), plan.ptr(names[2]), _p(dtab), N, _stream()))
+            dr1 = dtab
+        return (dx, dw, db, dr1, dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None, None, None, None)
 
 
 def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0, x_is_elu_out=False,
-           grad_is_preact=False):
-    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact)
+           grad_is_preact=False, res1_gather=None):
+    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact, res1_gather)
 
 
 def elu_mlp(x, w1, b1, w2, b2, act2=ACT_NONE, res1=None, res2=None, drop_p=0.0):
@@ -603,54 +621,81 @@ def row_gather(table, plan, names, rows):
 
 
 class TupleAttnFn(torch.autograd.Function):
+    """Attention over the tokens of every tuple.  With `gather = (plan, names)` the input is the QKV TABLE of distinct
+    token contents and the per-token gather is fused into the kernels (forward reads table rows through the token index;
+    backward writes per-token dqkv and pull-reduces it into the table in fixed order)."""
+
     @staticmethod
-    def forward(ctx, qkv, T, n_seq, n_heads):
+    def forward(ctx, qkv, T, n_seq, n_heads, gather=None):
         qkv = _req(qkv, "qkv").contiguous()
         E = qkv.shape[1] // 3
         out = torch.empty((T * n_seq, E), device=qkv.device, dtype=torch.float32)
-        _lib.check(_lib.lib().grappa_tuple_attn_fwd(T, n_seq, n_heads, E // n_heads, _p(qkv), _p(out), _stream()))
+        idx = gather[0].ptr(gather[1][0]) if gather is not None else None
+        _lib.check(_lib.lib().grappa_tuple_attn_fwd(T, n_seq, n_heads, E // n_heads, _p(qkv), idx, _p(out), _stream()))
         ctx.save_for_backward(qkv)
-        ctx.cfg = (T, n_seq, n_heads, E)
+        ctx.cfg = (T, n_seq, n_heads, E, gather)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         (qkv,) = ctx.saved_tensors
-        T, n_seq, n_heads, E = ctx.cfg
+        T, n_seq, n_heads, E, gather = ctx.cfg
         dout = dout.contiguous()
-        dqkv = torch.empty_like(qkv)
-        _lib.check(_lib.lib().grappa_tuple_attn_bwd(T, n_seq, n_heads, E // n_heads, _p(qkv), _p(dout), _p(dqkv), _stream()))
-        return dqkv, None, None, None
+        L = _lib.lib()
+        if gather is None:
+            dqkv = torch.empty_like(qkv)
+            _lib.check(L.grappa_tuple_attn_bwd(T, n_seq, n_heads, E // n_heads, _p(qkv), None, _p(dout), _p(dqkv), _stream()))
+            return dqkv, None, None, None, None
+        plan, names = gather
+        dtok = torch.empty((T * n_seq, 3 * E), device=qkv.device, dtype=torch.float32)
+        _lib.check(L.grappa_tuple_attn_bwd(T, n_seq, n_heads, E // n_heads, _p(qkv), plan.ptr(names[0]), _p(dout), _p(dtok), _stream()))
+        dtab = torch.empty_like(qkv)
+        _lib.check(L.grappa_row_gather_bwd(qkv.shape[0], 3 * E, _p(dtok), 3 * E, plan.ptr(names[1]), plan.ptr(names[2]), _p(dtab), 3 * E,
+                                           _stream()))
+        return dtab, None, None, None, None
 
 
-def tuple_attention(qkv, T, n_seq, n_heads):
-    return TupleAttnFn.apply(qkv, T, n_seq, n_heads)
+def tuple_attention(qkv, T, n_seq, n_heads, gather=None):
+    return TupleAttnFn.apply(qkv, T, n_seq, n_heads, gather)
 
 
 class TokenResidualFn(torch.autograd.Function):
+    """r = x3 + x * (col < F ? 2 : 1).  With `gather = (plan, names)`, `x` is the table of distinct token contents, read
+    through the token index inside the kernel; its gradient is pull-reduced per table row (fixed order) and scaled there,
+    so neither the gathered input nor its per-token gradient is ever written."""
+
     @staticmethod
-    def forward(ctx, x3, x, F):
+    def forward(ctx, x3, x, F, gather=None):
         x3 = _req(x3, "x3").contiguous()
         x = _req(x, "x").contiguous()
-        M, W = x.shape
-        r = torch.empty_like(x)
-        _lib.check(_lib.lib().grappa_token_residual(M, W, F, _p(x3), _p(x), _p(r), _stream()))
-        ctx.cfg = (M, W, F)
+        M, W = x3.shape
+        r = torch.empty_like(x3)
+        idx = gather[0].ptr(gather[1][0]) if gather is not None else None
+        _lib.check(_lib.lib().grappa_token_residual(M, W, F, _p(x3), _p(x), idx, _p(r), _stream()))
+        ctx.cfg = (M, W, F, gather, x.shape[0])
         return r
 
     @staticmethod
     def backward(ctx, dr):
-        M, W, F = ctx.cfg
+        M, W, F, gather, R = ctx.cfg
         dr = dr.contiguous()
         dx = None
+        L = _lib.lib()
         if ctx.needs_input_grad[1]:
-            dx = torch.empty_like(dr)
-            _lib.check(_lib.lib().grappa_token_residual_bwd(M, W, F, _p(dr), _p(dx), _stream()))
-        return dr, dx, None
+            if gather is None:
+                dx = torch.empty_like(dr)
+                _lib.check(L.grappa_token_residual_bwd(M, W, F, _p(dr), _p(dx), _stream()))
+            else:
+                plan, names = gather
+                tmp = torch.empty((R, W), device=dr.device, dtype=torch.float32)
+                _lib.check(L.grappa_row_gather_bwd(R, W, _p(dr), W, plan.ptr(names[1]), plan.ptr(names[2]), _p(tmp), W, _stream()))
+                dx = torch.empty_like(tmp)
+                _lib.check(L.grappa_token_residual_bwd(R, W, F, _p(tmp), _p(dx), _stream()))
+        return dr, dx, None, None
 
 
-def token_residual(x3, x, F):
-    return TokenResidualFn.apply(x3, x, F)
+def token_residual(x3, x, F, gather=None):
+    return TokenResidualFn.apply(x3, x, F, gather)
 
 
 class SymmPermuteFn(torch.autograd.Function):

@@ -61,12 +61,15 @@ int grappa_gemm(int layout, int64_t M, int64_t N, int64_t K,
  * call sites as grappa_gemm, for the layers whose B operand is a WEIGHT: B_hi / B_lo are its (N, K) bf16 planes, leading
  * dimension ldb16, made once per optimiser step by grappa_split_bf16 (the forward uses the planes of W, the dX GEMM the
  * planes of W^T, so both read K-major planes); A is fp32 and is split inside the kernel.  Epilogue, math_mode bits 8..15
- * (CTA budget) and workspace as grappa_gemm; elu_out / ld_eo as grappa_gemm_actgrad (may be NULL). */
+ * (CTA budget) and workspace as grappa_gemm; elu_out / ld_eo as grappa_gemm_actgrad (may be NULL).
+ * res1_idx (may be NULL): row m of the first residual is res1[res1_idx[m], :] -- the residual is a table of distinct token
+ * contents gathered inside the epilogue (readout: out_proj + LN(x) rows, interaction_parameters.py:184-189 fused away). */
 int grappa_gemm_bf16x3(int64_t M, int64_t N, int64_t K, const float* A, int64_t lda,
                        const uint16_t* B_hi, const uint16_t* B_lo, int64_t ldb16, float* C, int64_t ldc,
                        const float* bias, int act, const float* res1, int64_t ldr1, const float* res2, int64_t ldr2,
                        float drop_p, uint64_t seed, const uint64_t* seed_dev, int math_mode,
-                       float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo, void* stream);
+                       float* workspace, int64_t workspace_floats, const float* elu_out, int64_t ld_eo,
+                       const int32_t* res1_idx, void* stream);
 
 /* bf16 planes of a batch of weight matrices in one launch.  table (device, int64 x 4 per matrix): {offset of the matrix
  * in `params` (floats), rows, cols, offset of its planes in `planes` (uint16 elements)}; per matrix the planes are
@@ -188,14 +191,20 @@ int grappa_row_gather_bwd(int64_t table_rows, int D, const float* dX, int64_t ld
                           const int32_t* tok, float* dTable, int64_t ldt, void* stream);
 
 /* Self-attention over the n_seq <= 4 tokens of every tuple (nn.MultiheadAttention core, network_utils.py:123).
- * qkv: (T*n_seq, 3*E) = [q | k | v], E = n_heads*head_dim, head_dim 64.  out: (T*n_seq, E). */
-int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, float* out, void* stream);
-int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const float* dOut,
-                          float* dqkv, void* stream);
+ * qkv: (T*n_seq, 3*E) = [q | k | v], E = n_heads*head_dim, head_dim 64.  out: (T*n_seq, E).
+ * row_idx (may be NULL): token -> row of qkv; then qkv is the table of DISTINCT token contents (one row per (atom, pe),
+ * see grappa_pe_table_fwd) and the gather of interaction_parameters.py:184-189 happens inside the kernel: the
+ * (T*n_seq, 3*E) gathered tensor is never written.  dqkv is per token in both cases (T*n_seq, 3*E). */
+int grappa_tuple_attn_fwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const int32_t* row_idx,
+                          float* out, void* stream);
+int grappa_tuple_attn_bwd(int64_t T, int n_seq, int n_heads, int head_dim, const float* qkv, const int32_t* row_idx,
+                          const float* dOut, float* dqkv, void* stream);
 
 /* R = X3 + X * (col < F ? 2 : 1): the two input residuals around the transformer
- * (perm_equiv_transformer.py:165 and :75-77).  Backward: dX = dR * (col < F ? 2 : 1). */
-int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, float* R, void* stream);
+ * (perm_equiv_transformer.py:165 and :75-77).  Backward: dX = dR * (col < F ? 2 : 1).
+ * row_idx (may be NULL): token -> row of X; then X is the table of distinct token contents (width W) and the gather of
+ * the transformer input happens inside the kernel. */
+int grappa_token_residual(int64_t M, int W, int F, const float* X3, const float* X, const int32_t* row_idx, float* R, void* stream);
 int grappa_token_residual_bwd(int64_t M, int W, int F, const float* dR, float* dX, void* stream);
 
 /* Symmetriser input: rows (P*T, n_seq*W) with row p*T+t = concat_i X[t, perm[p][i], :]

@@ -352,13 +352,14 @@ def test_token_deduplication_is_exact_in_forward_and_consistent_in_backward(monk
         for m in model.modules():
             if isinstance(m, torch.nn.Dropout):
                 m.p = 0.0
-        calls = []
-        orig = ops.row_gather
-        monkeypatch.setattr(ops, "row_gather", lambda *a, **k: (calls.append(1), orig(*a, **k))[1])
+        calls = []            # the table path shows up as attention calls that gather from a table (no row_gather is left)
+        orig = ops.tuple_attention
+        monkeypatch.setattr(ops, "tuple_attention",
+                            lambda *a, **k: (calls.append(1) if k.get("gather") is not None else None, orig(*a, **k))[1])
         g = batch([S.trimer_molecule(seed=s, n_confs=3) for s in range(3)]).to(DEV)
         loss, g = train_loss(model, g)
         loss.backward()
-        monkeypatch.setattr(ops, "row_gather", orig)
+        monkeypatch.setattr(ops, "tuple_attention", orig)
         assert (len(calls) > 0) == dedup                      # bonds, angles and propers qualify at this size
         results[dedup] = (graph_params(g), float(loss), {n: p.grad.clone() for n, p in model.named_parameters() if p.grad is not None})
     for lvl in LEVELS:

@@ -241,6 +241,28 @@ def test_tuple_attention(n_seq):
     close(qg.grad, qr.grad, msg="tuple attn bwd", atol=2e-5 * float(qr.grad.abs().max()))
 
 
+def test_tuple_attention_with_the_qkv_gather_fused_is_bit_identical():
+    """The QKV rows of the (atom, pe) table are gathered inside the attention kernels: same output and same table
+    gradient, bit for bit, as materialising the gathered (T*n_seq, 3E) tensor first."""
+    from grappa_b200.graph import batch
+    from grappa_b200.plan import build_plan
+    g = batch([S.trimer_molecule(seed=s, n_confs=1) for s in (0, 1, 2)])
+    plan = build_plan(g).to(DEV)
+    for lvl, n_seq in (("n3", 3), ("n4", 4)):
+        names = ("tab_idx_" + lvl, "tab_ptr_" + lvl, "tab_tok_" + lvl)
+        T, R = plan.T[lvl], 2 * plan.n_atoms
+        gen = torch.Generator().manual_seed(n_seq)
+        tab = torch.randn(R, 1536, generator=gen).to(DEV)
+        gy = torch.randn(T * n_seq, 512, generator=gen).to(DEV)
+        a = tab.clone().requires_grad_(True)
+        out_a = ops.tuple_attention(ops.row_gather(a, plan, names, T * n_seq), T, n_seq, 8)
+        out_a.backward(gy)
+        b = tab.clone().requires_grad_(True)
+        out_b = ops.tuple_attention(b, T, n_seq, 8, gather=(plan, names))
+        out_b.backward(gy)
+        assert torch.equal(out_a, out_b) and torch.equal(a.grad, b.grad)
+
+
 def test_tuple_attention_matches_nn_multihead_attention():
     """The composition in_proj GEMM -> tuple attention -> out_proj GEMM equals nn.MultiheadAttention (seq-first)."""
     T, S_, E = 31, 3, 512
