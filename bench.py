@@ -70,7 +70,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
     def __exit__(self, *a):
         if self.proc is not None:
@@ -81,10 +81,13 @@ class ClockSampler:
             except Exception:
                 self.proc.kill()
 
-    def summary(self):
+    def summary(self, t0=None, t1=None):
+        """Samples taken inside [t0, t1] (the timed regions; nvidia-smi is started before the warm-up because its start-up
+        alone outlasts a 0.1 s timed region)."""
         sm, mx, reasons = [], [], set()
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        for ln in self.lines:
+        lines = [ln for ts_, ln in self.lines if (t0 is None or ts_ >= t0) and (t1 is None or ts_ <= t1 + 0.12)]
+        for ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -227,6 +230,8 @@ def main():
             torch.distributed.barrier()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local)
+    clocks.__enter__()
     # ---- warm-up (includes CUDA-graph capture after two eager steps) ----
     l0 = _lib.launch_count()
     ts.step(packed, load=True)
@@ -236,22 +241,7 @@ def main():
         ts.step(packed, load=True)
     barrier()
 
-    # ---- timed region 1: device-resident inputs ----
-    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clocks:
-        barrier()
-        start.record()
-        for _ in range(K):
-            loss = ts.step(packed, load=False)
-        end.record()
-        barrier()
-    ms = start.elapsed_time(end)
-    # ---- timed region 2: END TO END through the public training API with a DIFFERENT batch every step ----
-    # Every step draws 32 molecules from a device-resident molecule store (store.MoleculeStore, SURVEY.md §8f rank 3):
-    # the host work of a real loop (store.prepare: conformation choice, segment tables), the host->device copy of that
-    # step's inputs (the pinned segment tables; the molecules' own data already live in HBM) and the device->host read
-    # of the step's loss are all inside the timed region.  The loss of step k is consumed while step k+1 is being
-    # issued, as a training loop that logs its loss does.
+    # ---- set-up of the end-to-end region (molecule store, its batch shape captured), before any timing ----
     import numpy as np
     from grappa_b200 import synthetic as S
     from grappa_b200.store import MoleculeStore
@@ -261,6 +251,22 @@ def main():
     for ids in draws[:6]:                              # warm-up incl. CUDA-graph capture for this batch shape
         ts.step_from_store(store, ids)
     h2d_e2e = store.prepare(draws[0]).h2d_bytes
+    # ---- timed region 1: device-resident inputs ----
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_clock0 = time.time()
+    start.record()
+    for _ in range(K):
+        loss = ts.step(packed, load=False)
+    end.record()
+    barrier()
+    ms = start.elapsed_time(end)
+    # ---- timed region 2: END TO END through the public training API with a DIFFERENT batch every step ----
+    # Every step draws 32 molecules from a device-resident molecule store (store.MoleculeStore, SURVEY.md §8f rank 3):
+    # the host work of a real loop (store.prepare: conformation choice, segment tables), the host->device copy of that
+    # step's inputs (the pinned segment tables; the molecules' own data already live in HBM) and the device->host read
+    # of the step's loss are all inside the timed region.  The loss of step k is consumed while step k+1 is being
+    # issued, as a training loop that logs its loss does.
     barrier()
     start2, end2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start2.record()
@@ -293,6 +299,8 @@ def main():
     end3.record()
     barrier()
     ms3 = start3.elapsed_time(end3)
+    t_clock1 = time.time()
+    clocks.__exit__()
     t = torch.tensor([ms, ms2, ms3], device=dev, dtype=torch.float64)
     if world > 1:
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
@@ -315,7 +323,8 @@ def main():
                                               "h2d_bytes_per_step": packed.h2d_bytes}},
             "gpu_launches": int(launches_per_step * K), "final_loss": last}
     if rank == 0:
-        line["clocks"] = clocks.summary()
+        line["clocks"] = clocks.summary(t_clock0, t_clock1)
+        line["clocks"]["window"] = "device-resident + both end-to-end timed regions (back to back, all under load)"
     if world > 1:
         line["dp_check"] = dp_check(ts, world, rank, dev)
     line["strong_scaling_global256"] = strong_scaling(ts, world, rank, dev, K)
