@@ -44,6 +44,9 @@ PROTOTYPES = {
     "grappa_token_residual_bwd": (I, [I64, I, I, P, P, P]),
     "grappa_symm_permute_fwd": (I, [I64, I, I, I, P, P, P, P]),
     "grappa_symm_permute_bwd": (I, [I64, I, I, I, P, P, P, P]),
+    "grappa_symm_ln_fwd": (I, [I64, I, I, I, P, P, P, P, P, P, P, P]),
+    "grappa_symm_ln_bwd_scratch_floats": (I64, [I64, I, I]),
+    "grappa_symm_ln_bwd": (I, [I64, I, I, I, P, P, P, P, P, P, P, P, P, P, P]),
     "grappa_readout_finalize_fwd": (I, [I, I64, I, I, P, P, P, P, P, I, I, P, P, P, P]),
     "grappa_readout_finalize_bwd": (I, [I, I64, I, I, P, P, P, P, P, I, I, P, P, P, P]),
     "grappa_energy_plan_build": (I, [I64, I64, P, P, I64, P, I64, P, I64, P, I64, I, I, P, P, P, P, P]),
@@ -143,7 +146,7 @@ class _ProfiledLib:
     def __getattr__(self, name):
         fn = getattr(self._h, name)
         if not name.startswith("grappa_") or name in ("grappa_last_error", "grappa_launch_count", "grappa_abi_version",
-                                                       "grappa_colsum_scratch_floats", "grappa_layernorm_bwd_scratch_floats",
+                                                       "grappa_colsum_scratch_floats", "grappa_layernorm_bwd_scratch_floats", "grappa_symm_ln_bwd_scratch_floats",
                                                        "grappa_csr_build", "grappa_energy_plan_build", "grappa_enumerate_tuples", "grappa_plan_build",
                                                        "grappa_plan_fill", "grappa_plan_free"):
             return fn

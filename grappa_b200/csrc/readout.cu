@@ -305,6 +305,134 @@ __global__ void symm_permute_bwd_kernel(int64_t T, int n_seq, int W, int P, Perm
     }
 }
 
+// -------------------------------------------------------------------- fused symmetriser input (permute + LayerNorm)
+// perm_equiv_transformer.py:266-279 stacks the permuted copies of every tuple's token row (P*T, n_seq*W) and the first
+// FeedForwardLayer normalises each copy (network_utils.py:46).  All permutations of a tuple hold the same multiset of
+// values, so mean / rstd are computed ONCE per tuple and the permuted, normalised, affine-transformed rows are written
+// directly: the un-normalised permuted copy never exists and the statistics pass runs over T rows instead of P*T.
+//   Y[p*T + t, i*W + c] = (X[t, perm[p][i]*W + c] - mean_t) * rstd_t * gamma[i*W + c] + beta[i*W + c]
+// One warp per tuple; the row (<= 8 KB) stays L1-resident across the passes.
+constexpr float kSymmLnEps = 1e-5f;
+
+__global__ void __launch_bounds__(256) symm_ln_fwd_kernel(int64_t T, int n_seq, int W, int P, PermTable pt,
+                                                          const float* __restrict__ X, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float* __restrict__ Y,
+                                                          float* __restrict__ mean, float* __restrict__ rstd) {
+    const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (t >= T) return;
+    const int W4 = W / 4, D4 = n_seq * W4, D = n_seq * W;
+    const float4* x4 = reinterpret_cast<const float4*>(X) + t * D4;
+    float s = 0.f, v = 0.f;
+    for (int i = lane; i < D4; i += 32) { const float4 q = x4[i]; s += (q.x + q.y) + (q.z + q.w); }
+    const float mu = warp_sum(s) / (float)D;
+    for (int i = lane; i < D4; i += 32) {
+        const float4 q = x4[i];
+        const float a = q.x - mu, b = q.y - mu, c = q.z - mu, d = q.w - mu;
+        v += (a * a + b * b) + (c * c + d * d);
+    }
+    const float rs = rsqrtf(warp_sum(v) / (float)D + kSymmLnEps);
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    const float4* b4 = reinterpret_cast<const float4*>(beta);
+    for (int p = 0; p < P; ++p) {
+        float4* y4 = reinterpret_cast<float4*>(Y) + ((int64_t)p * T + t) * D4;
+        for (int i = lane; i < D4; i += 32) {                   // i = destination chunk
+            const int pos = i / W4, off = i - pos * W4;
+            const float4 q = x4[pt.perm[p][pos] * W4 + off], g = __ldg(g4 + i), bb = __ldg(b4 + i);
+            y4[i] = make_float4((q.x - mu) * rs * g.x + bb.x, (q.y - mu) * rs * g.y + bb.y, (q.z - mu) * rs * g.z + bb.z,
+                                (q.w - mu) * rs * g.w + bb.w);
+        }
+    }
+    if (lane == 0) { mean[t] = mu; rstd[t] = rs; }
+}
+
+// dX[t, s] = rstd (g_s - mean(g) - xhat_s mean(g xhat)),  g_s = sum_p dY[p*T + t, dest_p(s)] * gamma[dest_p(s)]
+__global__ void __launch_bounds__(256) symm_ln_bwd_dx_kernel(int64_t T, int n_seq, int W, int P, PermTable pt,
+                                                             const float* __restrict__ dY, const float* __restrict__ X,
+                                                             const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                             const float* __restrict__ rstd, float* __restrict__ dX) {
+    const int64_t t = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (t >= T) return;
+    const int W4 = W / 4, D4 = n_seq * W4, D = n_seq * W;
+    const float4* x4 = reinterpret_cast<const float4*>(X) + t * D4;
+    const float4* g4 = reinterpret_cast<const float4*>(gamma);
+    const float mu = mean[t], rs = rstd[t];
+    auto grad = [&](int i) {                                     // i = source chunk
+        const int blk = i / W4, off = i - blk * W4;
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int p = 0; p < P; ++p) {
+            const int d = pt.inv[p][blk] * W4 + off;
+            const float4 dy = __ldg(reinterpret_cast<const float4*>(dY) + ((int64_t)p * T + t) * D4 + d), ga = __ldg(g4 + d);
+            g.x = fmaf(dy.x, ga.x, g.x); g.y = fmaf(dy.y, ga.y, g.y); g.z = fmaf(dy.z, ga.z, g.z); g.w = fmaf(dy.w, ga.w, g.w);
+        }
+        return g;
+    };
+    float s1 = 0.f, s2 = 0.f;
+    for (int i = lane; i < D4; i += 32) {
+        const float4 g = grad(i), q = x4[i];
+        s1 += (g.x + g.y) + (g.z + g.w);
+        s2 += (g.x * ((q.x - mu) * rs) + g.y * ((q.y - mu) * rs)) + (g.z * ((q.z - mu) * rs) + g.w * ((q.w - mu) * rs));
+    }
+    s1 = warp_sum(s1) / (float)D;
+    s2 = warp_sum(s2) / (float)D;
+    float4* o4 = reinterpret_cast<float4*>(dX) + t * D4;
+    for (int i = lane; i < D4; i += 32) {
+        const float4 g = grad(i), q = x4[i];
+        o4[i] = make_float4(rs * (g.x - s1 - (q.x - mu) * rs * s2), rs * (g.y - s1 - (q.y - mu) * rs * s2),
+                            rs * (g.z - s1 - (q.z - mu) * rs * s2), rs * (g.w - s1 - (q.w - mu) * rs * s2));
+    }
+}
+
+// dgamma[d] = sum_p sum_t dY[p*T + t, d] xhat[t, src_p(d)], dbeta[d] = sum_p sum_t dY[p*T + t, d]: partial sums over a
+// chunk of tuples per CTA (warps interleave tuples, combined in warp order), then a fixed-order sum over the chunks.
+__global__ void __launch_bounds__(256) symm_ln_affine_stage1_kernel(int64_t T, int n_seq, int W, int P, PermTable pt,
+                                                                    const float* __restrict__ dY, const float* __restrict__ X,
+                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                    int rows_per_chunk, float* __restrict__ part_g,
+                                                                    float* __restrict__ part_b) {
+    __shared__ float4 sh[2][8][32];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int W4 = W / 4, D4 = n_seq * W4;
+    const int d4 = blockIdx.x * 32 + lane;
+    const bool ok = d4 < D4;
+    const int pos = ok ? d4 / W4 : 0, off = ok ? d4 - pos * W4 : 0;
+    const int64_t t0 = (int64_t)blockIdx.y * rows_per_chunk, t1 = min(T, t0 + rows_per_chunk);
+    float4 sg = make_float4(0.f, 0.f, 0.f, 0.f), sb = sg;
+    if (ok) {
+        for (int64_t t = t0 + wrp; t < t1; t += 8) {
+            const float mu = __ldg(mean + t), rs = __ldg(rstd + t);
+            for (int p = 0; p < P; ++p) {
+                const float4 dy = __ldg(reinterpret_cast<const float4*>(dY) + ((int64_t)p * T + t) * D4 + d4);
+                const float4 q = __ldg(reinterpret_cast<const float4*>(X) + t * D4 + pt.perm[p][pos] * W4 + off);
+                sb.x += dy.x; sb.y += dy.y; sb.z += dy.z; sb.w += dy.w;
+                sg.x = fmaf(dy.x, (q.x - mu) * rs, sg.x); sg.y = fmaf(dy.y, (q.y - mu) * rs, sg.y);
+                sg.z = fmaf(dy.z, (q.z - mu) * rs, sg.z); sg.w = fmaf(dy.w, (q.w - mu) * rs, sg.w);
+            }
+        }
+    }
+    sh[0][wrp][lane] = sg; sh[1][wrp][lane] = sb;
+    __syncthreads();
+    if (wrp < 2 && ok) {
+        float4 a = sh[wrp][0][lane];
+#pragma unroll
+        for (int j = 1; j < 8; ++j) { const float4 u = sh[wrp][j][lane]; a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w; }
+        float* part = wrp == 0 ? part_g : part_b;
+        reinterpret_cast<float4*>(part + (int64_t)blockIdx.y * n_seq * W)[d4] = a;
+    }
+}
+
+__global__ void __launch_bounds__(256) symm_ln_affine_stage2_kernel(int64_t R, int64_t D, const float* __restrict__ part_g,
+                                                                    const float* __restrict__ part_b, float* __restrict__ dgamma,
+                                                                    float* __restrict__ dbeta) {
+    const int64_t col = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= D) return;
+    const float* part = blockIdx.y == 0 ? part_g : part_b;
+    float s = 0.f;
+    for (int64_t r = 0; r < R; ++r) s += part[r * D + col];
+    (blockIdx.y == 0 ? dgamma : dbeta)[col] = s;
+}
+
 // ------------------------------------------------------------------------------------------ finalize ----------
 
 struct FinalizeConsts {
@@ -541,6 +669,51 @@ extern "C" int grappa_symm_permute_bwd(int64_t T, int n_seq, int W, int P, const
     GRAPPA_CHECK_ARG(dY && dX, "null pointer");
     symm_permute_bwd_kernel<<<grid_for(T * n_seq * (W / 4)), 256, 0, (cudaStream_t)stream>>>(T, n_seq, W, P, pt, dY, dX);
     GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+static inline int symm_ln_rows_per_chunk(int64_t T) { return (int)std::max<int64_t>(8, ceil_div(ceil_div(T, 37), 8) * 8); }   // ~37 chunks x 16 column blocks
+
+extern "C" int64_t grappa_symm_ln_bwd_scratch_floats(int64_t T, int n_seq, int W) {
+    return 2 * ceil_div(std::max<int64_t>(T, 1), symm_ln_rows_per_chunk(T)) * n_seq * W;
+}
+
+extern "C" int grappa_symm_ln_fwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* X, const float* gamma,
+                                  const float* beta, float* Y, float* mean, float* rstd, void* stream) {
+    PermTable pt;
+    if (int rc = make_perm_table(n_seq, P, perm, pt)) return rc;
+    GRAPPA_CHECK_ARG(T >= 0 && W > 0 && W % 4 == 0, "W must be a multiple of 4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(X && gamma && beta && Y && mean && rstd, "null pointer");
+    symm_ln_fwd_kernel<<<(unsigned)ceil_div(T * 32, 256), 256, 0, (cudaStream_t)stream>>>(T, n_seq, W, P, pt, X, gamma, beta, Y, mean, rstd);
+    GRAPPA_CHECK_LAUNCH();
+    return 0;
+}
+
+extern "C" int grappa_symm_ln_bwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* dY, const float* X,
+                                  const float* gamma, const float* mean, const float* rstd, float* dX, float* dgamma, float* dbeta,
+                                  float* scratch, void* stream) {
+    PermTable pt;
+    if (int rc = make_perm_table(n_seq, P, perm, pt)) return rc;
+    GRAPPA_CHECK_ARG(T >= 0 && W > 0 && W % 4 == 0, "W must be a multiple of 4");
+    if (T == 0) return 0;
+    GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && (dX || dgamma), "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dX) {
+        symm_ln_bwd_dx_kernel<<<(unsigned)ceil_div(T * 32, 256), 256, 0, st>>>(T, n_seq, W, P, pt, dY, X, gamma, mean, rstd, dX);
+        GRAPPA_CHECK_LAUNCH();
+    }
+    if (dgamma || dbeta) {
+        GRAPPA_CHECK_ARG(dgamma && dbeta && scratch, "dgamma, dbeta and scratch must be given together");
+        const int rpc = symm_ln_rows_per_chunk(T);
+        const int64_t R = ceil_div(T, rpc), D = (int64_t)n_seq * W;
+        float* pg = scratch;
+        float* pb = scratch + R * D;
+        symm_ln_affine_stage1_kernel<<<dim3((unsigned)ceil_div(D / 4, 32), (unsigned)R), 256, 0, st>>>(T, n_seq, W, P, pt, dY, X, mean, rstd, rpc, pg, pb);
+        GRAPPA_CHECK_LAUNCH();
+        symm_ln_affine_stage2_kernel<<<dim3((unsigned)ceil_div(D, 256), 2), 256, 0, st>>>(R, D, pg, pb, dgamma, dbeta);
+        GRAPPA_CHECK_LAUNCH();
+    }
     return 0;
 }
 

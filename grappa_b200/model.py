@@ -15,6 +15,7 @@ Module names mirror the reference files they replace:
   ToPositive / ToRange                  models/final_layer.py:11-97
 """
 import copy
+import os
 import math
 from typing import Dict, List, Union
 
@@ -59,6 +60,7 @@ _WRITER_STREAMS = {}
 # distinct (atom, pe) row instead of once per token whenever there are at least DEDUP_RATIO times more tokens than rows.
 DEDUP_TOKENS = True
 DEDUP_RATIO = 1.5
+FUSE_SYMM_LN = os.environ.get("GRAPPA_FUSE_SYMM_LN", "1") != "0"     # training: permute + first LayerNorm of the symmetriser in one kernel
 FOLD_SYMMETRISER = True       # inference: the symmetriser's permutations folded into weight views (Symmetriser._forward_folded)
 WRITER_STREAM_PRIORITIES = (-1, -1, -2, -1)
 
@@ -355,8 +357,17 @@ class Symmetriser(nn.Module):
         which is fused with the range maps in the writers.  Returns (n_perm*T, out_feats)."""
         if FOLD_SYMMETRISER and not torch.is_grad_enabled() and T > 0:
             return self._forward_folded(x, T)
-        rows = ops.symm_permute(x, T, self.n_seq, self._perms_host)
-        for layer in self.mlp:
+        first = self.mlp[0]
+        if FUSE_SYMM_LN and T > 0 and not first.skip and x.shape[1] % 4 == 0:
+            # permuted copies + the first layer's LayerNorm in one kernel (statistics once per tuple, no un-normalised copy)
+            n = ops.symm_layer_norm(x, first.norm1.weight, first.norm1.bias, T, self.n_seq, self._perms_host)
+            rows = ops.elu_mlp(n, first.linear1.weight, first.linear1.bias, first.linear2.weight, first.linear2.bias,
+                               drop_p=first.dropout.p if self.training else 0.0)
+            rest = list(self.mlp)[1:]
+        else:
+            rows = ops.symm_permute(x, T, self.n_seq, self._perms_host)
+            rest = list(self.mlp)
+        for layer in rest:
             rows = layer(rows)
         return rows
 

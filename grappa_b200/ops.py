@@ -719,6 +719,55 @@ class SymmPermuteFn(torch.autograd.Function):
         return dx, None, None, None
 
 
+class SymmLayerNormFn(torch.autograd.Function):
+    """The symmetriser's permuted copies with the first LayerNorm fused in (grappa_symm_ln_fwd / _bwd): statistics once per
+    tuple, the un-normalised permuted copy is never written."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, T, n_seq, perms):
+        x = _req(x, "x").contiguous()
+        W = x.shape[1]
+        P = len(perms)
+        flat = (ctypes.c_int32 * (P * n_seq))(*[int(v) for p in perms for v in p])
+        y = torch.empty((P * T, n_seq * W), device=x.device, dtype=torch.float32)
+        stats = torch.empty((2, max(T, 1)), device=x.device, dtype=torch.float32)
+        _lib.check(_lib.lib().grappa_symm_ln_fwd(T, n_seq, W, P, flat, _p(x), _p(gamma), _p(beta), _p(y), _p(stats[0]), _p(stats[1]),
+                                                 _stream()))
+        ctx.save_for_backward(x, gamma, stats)
+        ctx.cfg = (T, n_seq, W, P, flat)
+        ctx.sink_ids = (id(gamma), id(beta))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, stats = ctx.saved_tensors
+        T, n_seq, W, P, flat = ctx.cfg
+        L = _lib.lib()
+        dy = dy.contiguous()
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        need_affine = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        dg = db = scratch = None
+        sunk = False
+        if need_affine:
+            sink = GRAD_SINK
+            tg = sink.get(ctx.sink_ids[0]) if sink is not None else None
+            tb = sink.get(ctx.sink_ids[1]) if sink is not None else None
+            sunk = tg is not None and tb is not None
+            D = n_seq * W
+            dg = tg if sunk else torch.empty((D,), device=dy.device, dtype=torch.float32)
+            db = tb if sunk else torch.empty((D,), device=dy.device, dtype=torch.float32)
+            scratch = torch.empty((int(L.grappa_symm_ln_bwd_scratch_floats(T, n_seq, W)),), device=dy.device, dtype=torch.float32)
+        _lib.check(L.grappa_symm_ln_bwd(T, n_seq, W, P, flat, _p(dy), _p(x), _p(gamma), _p(stats[0]), _p(stats[1]), _p(dx), _p(dg), _p(db),
+                                        _p(scratch), _stream()))
+        if sunk:
+            dg = db = None
+        return dx, dg, db, None, None, None
+
+
+def symm_layer_norm(x, gamma, beta, T, n_seq, perms):
+    return SymmLayerNormFn.apply(x, gamma, beta, T, n_seq, perms)
+
+
 def symm_permute(x, T, n_seq, perms):
     return SymmPermuteFn.apply(x, T, n_seq, perms)
 

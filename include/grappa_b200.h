@@ -214,6 +214,21 @@ int grappa_symm_permute_fwd(int64_t T, int n_seq, int W, int P, const int32_t* p
 int grappa_symm_permute_bwd(int64_t T, int n_seq, int W, int P, const int32_t* perm /*HOST*/, const float* dY,
                             float* dX, void* stream);
 
+/* Symmetriser input with the first LayerNorm fused in (training path): the permuted copies of every tuple's token row
+ * (perm_equiv_transformer.py:266-279) normalised by the first FeedForwardLayer's LayerNorm (network_utils.py:46) in ONE
+ * pass.  All permutations of a tuple hold the same values, so mean / rstd are computed once per tuple (T rows instead of
+ * P*T) and the un-normalised permuted copy is never written:
+ *   Y[p*T + t, i*W + c] = (X[t, perm[p][i]*W + c] - mean_t) * rstd_t * gamma[i*W + c] + beta[i*W + c]
+ * X: (T*n_seq, W) tuple-major tokens, gamma / beta: (n_seq*W), Y: (P*T, n_seq*W), mean / rstd: (T) saved for backward.
+ * Backward: dX (T*n_seq, W), dgamma / dbeta (n_seq*W); scratch of grappa_symm_ln_bwd_scratch_floats floats; dX or
+ * (dgamma, dbeta, scratch) may be NULL. */
+int grappa_symm_ln_fwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* X, const float* gamma,
+                       const float* beta, float* Y, float* mean, float* rstd, void* stream);
+int64_t grappa_symm_ln_bwd_scratch_floats(int64_t T, int n_seq, int W);
+int grappa_symm_ln_bwd(int64_t T, int n_seq, int W, int P, const int32_t* perm, const float* dY, const float* X,
+                       const float* gamma, const float* mean, const float* rstd, float* dX, float* dgamma, float* dbeta,
+                       float* scratch, void* stream);
+
 /* Sum over permutations (perm_equiv_transformer.py:288-292) fused with the range maps
  * (final_layer.py:48-52, 91-97; interaction_parameters.py:276-288, 382-395, 586-611; network_utils.py:147-148).
  * S: (P*T, n_out) symmetriser outputs; prefactor: HOST (P).

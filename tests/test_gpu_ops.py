@@ -263,6 +263,32 @@ def test_tuple_attention_with_the_qkv_gather_fused_is_bit_identical():
         assert torch.equal(out_a, out_b) and torch.equal(a.grad, b.grad)
 
 
+@pytest.mark.parametrize("n_seq,perms", [(2, [[0, 1], [1, 0]]), (3, [[0, 1, 2], [2, 1, 0]]), (4, [[0, 1, 2, 3], [3, 1, 2, 0]])])
+def test_symmetriser_permute_with_fused_layer_norm(n_seq, perms):
+    """grappa_symm_ln_*: permuted copies + LayerNorm over the (n_seq * W) row in one kernel, against
+    F.layer_norm of the explicitly stacked permutations (forward, dX, dgamma, dbeta)."""
+    T, W = 333, 512
+    gen = torch.Generator().manual_seed(n_seq)
+    x = torch.randn(T * n_seq, W, generator=gen) * 1.7 + 0.3
+    gamma, beta = 1 + 0.1 * torch.randn(n_seq * W, generator=gen), 0.1 * torch.randn(n_seq * W, generator=gen)
+    gy = torch.randn(len(perms) * T, n_seq * W, generator=gen)
+    xr, gr, br = [t.clone().double().requires_grad_(True) for t in (x, gamma, beta)]
+    x3 = xr.view(T, n_seq, W)
+    stacked = torch.cat([x3[:, p, :].reshape(T, n_seq * W) for p in perms], dim=0)
+    ref = F.layer_norm(stacked, (n_seq * W,), gr, br)
+    ref.backward(gy.double())
+    xg, gg, bg = [t.clone().to(DEV).requires_grad_(True) for t in (x, gamma, beta)]
+    out = ops.symm_layer_norm(xg, gg, bg, T, n_seq, perms)
+    out.backward(gy.to(DEV))
+    close(out, ref, msg="symm ln fwd")
+    close(xg.grad, xr.grad, msg="symm ln dx", atol=2e-5 * float(xr.grad.abs().max()))
+    close(gg.grad, gr.grad, msg="symm ln dgamma", atol=2e-5 * float(gr.grad.abs().max()))
+    close(bg.grad, br.grad, msg="symm ln dbeta", atol=2e-5 * float(br.grad.abs().max()))
+    # identical to the two-kernel path up to the summation order of the statistics
+    two = ops.layer_norm(ops.symm_permute(xg.detach(), T, n_seq, perms), gg.detach(), bg.detach())
+    assert float((two - out.detach()).abs().max()) < 2e-5
+
+
 def test_tuple_attention_matches_nn_multihead_attention():
     """The composition in_proj GEMM -> tuple attention -> out_proj GEMM equals nn.MultiheadAttention (seq-first)."""
     T, S_, E = 31, 3, 512
