@@ -407,8 +407,80 @@ extern "C" int grappa_layernorm_fwd(int64_t M, int64_t D, const float* X, int64_
     return 0;
 }
 
+// dX and the stage-1 partial sums of dgamma / dbeta in ONE pass over dY and X (D = 32 * 4 * NV <= 512): a CTA owns a
+// chunk of rows, its 8 warps interleave them; every lane keeps the row's values in registers (dY and X are read once),
+// accumulates its columns' dgamma / dbeta partials over the warp's rows, and the 8 warps' partials are combined in warp
+// order through shared memory.  The separate reduction pass re-read both tensors (2 of the 5 tensor passes of the op).
+template <int NV>
+__global__ void __launch_bounds__(256) layernorm_bwd_fused_kernel(int64_t M, const float* __restrict__ dY, int64_t lddy,
+                                                                  const float* __restrict__ X, int64_t ldx,
+                                                                  const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                                  const float* __restrict__ rstd, float* __restrict__ dX, int64_t lddx,
+                                                                  int rows_per_chunk, float* __restrict__ part_g,
+                                                                  float* __restrict__ part_b) {
+    constexpr int D = 128 * NV;
+    __shared__ float4 sh[8][32 * NV];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
+    float4 g[NV], ag[NV], ab[NV];
+#pragma unroll
+    for (int m = 0; m < NV; ++m) {
+        g[m] = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * m);
+        ag[m] = make_float4(0.f, 0.f, 0.f, 0.f); ab[m] = ag[m];
+    }
+    for (int64_t row = r0 + wrp; row < r1; row += 8) {
+        const float4* x4 = reinterpret_cast<const float4*>(X + row * ldx);
+        const float4* d4 = reinterpret_cast<const float4*>(dY + row * lddy);
+        const float mu = mean[row], rs = rstd[row];
+        float4 xh[NV], dy[NV];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int m = 0; m < NV; ++m) {
+            const float4 t = x4[lane + 32 * m];
+            dy[m] = d4[lane + 32 * m];
+            xh[m] = make_float4((t.x - mu) * rs, (t.y - mu) * rs, (t.z - mu) * rs, (t.w - mu) * rs);
+            const float a = dy[m].x * g[m].x, b = dy[m].y * g[m].y, c = dy[m].z * g[m].z, e = dy[m].w * g[m].w;
+            s1 += (a + b) + (c + e);
+            s2 += (a * xh[m].x + b * xh[m].y) + (c * xh[m].z + e * xh[m].w);
+            ab[m].x += dy[m].x; ab[m].y += dy[m].y; ab[m].z += dy[m].z; ab[m].w += dy[m].w;
+            ag[m].x = fmaf(dy[m].x, xh[m].x, ag[m].x); ag[m].y = fmaf(dy[m].y, xh[m].y, ag[m].y);
+            ag[m].z = fmaf(dy[m].z, xh[m].z, ag[m].z); ag[m].w = fmaf(dy[m].w, xh[m].w, ag[m].w);
+        }
+        s1 = warp_sum(s1) / (float)D;
+        s2 = warp_sum(s2) / (float)D;
+        float4* o4 = reinterpret_cast<float4*>(dX + row * lddx);
+#pragma unroll
+        for (int m = 0; m < NV; ++m)
+            o4[lane + 32 * m] = make_float4(rs * (dy[m].x * g[m].x - s1 - xh[m].x * s2), rs * (dy[m].y * g[m].y - s1 - xh[m].y * s2),
+                                            rs * (dy[m].z * g[m].z - s1 - xh[m].z * s2), rs * (dy[m].w * g[m].w - s1 - xh[m].w * s2));
+    }
+#pragma unroll 1
+    for (int which = 0; which < 2; ++which) {
+#pragma unroll
+        for (int m = 0; m < NV; ++m) sh[wrp][lane + 32 * m] = which == 0 ? ag[m] : ab[m];
+        __syncthreads();
+        float* part = (which == 0 ? part_g : part_b) + (int64_t)blockIdx.x * D;
+        for (int i = threadIdx.x; i < 32 * NV; i += 256) {
+            float4 a = sh[0][i];
+#pragma unroll
+            for (int j = 1; j < 8; ++j) { const float4 u = sh[j][i]; a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w; }
+            reinterpret_cast<float4*>(part)[i] = a;
+        }
+        __syncthreads();
+    }
+}
+
+// rows per CTA of the fused kernel: about two waves of CTAs, multiple of 8 (the warps interleave rows)
+static inline int ln_fused_rows_per_chunk(int64_t M) {
+    const int64_t chunks = std::max<int64_t>(1, std::min<int64_t>(296, ceil_div(M, 8)));
+    return (int)(ceil_div(ceil_div(std::max<int64_t>(M, 1), chunks), 8) * 8);
+}
+static inline bool ln_fused_ok(int64_t D) { return D == 128 || D == 256 || D == 384 || D == 512; }
+
 extern "C" int64_t grappa_layernorm_bwd_scratch_floats(int64_t M, int64_t D) {
-    return 2 * std::max(col_chunks(M, D), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk)) * D;
+    int64_t R = std::max(col_chunks(M, D), ceil_div(std::max<int64_t>(M, 1), kRowsPerChunk));
+    if (ln_fused_ok(D)) R = std::max(R, ceil_div(std::max<int64_t>(M, 1), ln_fused_rows_per_chunk(M)));
+    return 2 * R * D;
 }
 
 extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64_t lddy, const float* X, int64_t ldx,
@@ -418,6 +490,23 @@ extern "C" int grappa_layernorm_bwd(int64_t M, int64_t D, const float* dY, int64
     GRAPPA_CHECK_ARG(dY && X && gamma && mean && rstd && (dX || dgamma), "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     const bool vec = D % 4 == 0 && ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0 && al16(X) && al16(dY) && al16(dX) && al16(gamma);
+    if (M > 0 && dX != nullptr && dgamma != nullptr && vec && ln_fused_ok(D)) {      // everything in one pass over dY and X
+        GRAPPA_CHECK_ARG(dbeta && scratch, "dgamma, dbeta and scratch must be given together");
+        const int rpc = ln_fused_rows_per_chunk(M);
+        const int64_t R = ceil_div(M, rpc);
+        float* pg = scratch;
+        float* pb = scratch + R * D;
+        switch (D / 128) {
+            case 1: layernorm_bwd_fused_kernel<1><<<(unsigned)R, 256, 0, st>>>(M, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx, rpc, pg, pb); break;
+            case 2: layernorm_bwd_fused_kernel<2><<<(unsigned)R, 256, 0, st>>>(M, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx, rpc, pg, pb); break;
+            case 3: layernorm_bwd_fused_kernel<3><<<(unsigned)R, 256, 0, st>>>(M, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx, rpc, pg, pb); break;
+            default: layernorm_bwd_fused_kernel<4><<<(unsigned)R, 256, 0, st>>>(M, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx, rpc, pg, pb); break;
+        }
+        GRAPPA_CHECK_LAUNCH();
+        colreduce_stage2_vec_kernel<<<dim3((unsigned)ceil_div(D, 32), 2), 256, 0, st>>>(R, D, pg, pb, dgamma, dbeta);
+        GRAPPA_CHECK_LAUNCH();
+        return 0;
+    }
     if (M > 0 && dX != nullptr) {          // dX == NULL: only the affine reductions (issued on a side stream by the caller)
         const unsigned grid = (unsigned)ceil_div(M * 32, 256);
         if (vec) layernorm_bwd_dx_kernel<true><<<grid, 256, 0, st>>>(M, (int)D, dY, lddy, X, ldx, gamma, mean, rstd, dX, lddx);
