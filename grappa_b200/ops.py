@@ -21,6 +21,7 @@ ACT_NONE, ACT_ELU = 0, 1
 # (views of the trainer's flat gradient buffer) and autograd sees None, i.e. no per-parameter accumulate kernels.
 # Valid because every parameter of the model is used exactly once per forward.
 GRAD_SINK = None
+FUSE_SKIP_GRAD = _os.environ.get("GRAPPA_FUSE_SKIP_GRAD", "1") != "0"    # Linear-ELU-Linear + skip: the skip's gradient added in the first layer's dX GEMM epilogue
 FUSE_ELU_GRAD = _os.environ.get("GRAPPA_FUSE_ELU_GRAD", "1") != "0"      # Linear-ELU-Linear blocks: ELU' of the hidden tensor in the dX GEMM epilogue (see LinearFn)
 # With a gradient sink nothing downstream in autograd consumes parameter gradients, so the weight-gradient GEMM, the
 # bias column sum and the LayerNorm affine reductions are issued on a side stream and overlap with the activation-
@@ -304,7 +305,11 @@ class LinearFn(torch.autograd.Function):
                     pre-activation."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out=False, grad_is_preact=False, res1_gather=None):
+    def forward(ctx, x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out=False, grad_is_preact=False, res1_gather=None,
+                dx_add=None, res1_grad_to=None):
+        # dx_add / res1_grad_to (a shared _GradHolder): in y = W2 f(W1 x) + x the skip's gradient reaches x twice; the second
+        # layer hands dL/dy to the holder instead of returning it for res1, and the first layer's dX GEMM adds it in its
+        # epilogue -- one fused add instead of an autograd accumulation kernel over the (rows, features) tensor
         # res1_gather = (plan, names): res1 is a TABLE of distinct token contents; row m of the residual is
         # res1[idx[m]], gathered inside the GEMM epilogue (its gradient is pull-reduced per table row in backward)
         x, lda = _rows2d(x, "x")
@@ -350,6 +355,7 @@ class LinearFn(torch.autograd.Function):
             raise ValueError("grad_is_preact needs a plain ELU layer (no dropout, no residual)")
         ctx.cfg = (act, float(drop_p), seed, seed_dev, N, ldc, bias is not None, res1 is not None, res2 is not None)
         ctx.flags = (bool(x_is_elu_out), bool(grad_is_preact))
+        ctx.dx_add, ctx.res1_grad_to = dx_add, res1_grad_to
         ctx.sink_ids = (id(weight), id(bias))
         return y
 
@@ -403,14 +409,21 @@ class LinearFn(torch.autograd.Function):
                 param_grads()
         else:
             param_grads()
+        extra = ldx_extra = None
+        if ctx.dx_add is not None and ctx.dx_add.value is not None:      # the skip's gradient, handed over by the second layer
+            extra, ldx_extra = _rows2d(ctx.dx_add.value, "skip gradient")
+            ctx.dx_add.value = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty((M, K), device=dy.device, dtype=torch.float32)
             if ctx.planes is not None and _bf16_ok(dz, lddz, M, K, N):     # dx = dz W: the planes of W^T are K-major for it
-                gemm_bf16(M, K, N, dz, lddz, ctx.planes.nn, dx, K, elu_out=x if x_is_elu_out else None, ld_eo=lda if x_is_elu_out else 0)
+                gemm_bf16(M, K, N, dz, lddz, ctx.planes.nn, dx, K, res1=extra, ldr1=ldx_extra or 0,
+                          elu_out=x if x_is_elu_out else None, ld_eo=lda if x_is_elu_out else 0)
             elif x_is_elu_out:
                 gemm_actgrad(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, x, lda, b_lo=ctx.w_lo)
+                if extra is not None:
+                    dx = dx + extra
             else:
-                gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, b_lo=ctx.w_lo)
+                gemm(1, M, K, N, dz, lddz, w, w.stride(0), dx, K, res1=extra, ldr1=ldx_extra or 0, b_lo=ctx.w_lo)
         if b_sunk:
             db = None
         dr = dy if ldc == N else dy[:, :N]
@@ -421,19 +434,32 @@ class LinearFn(torch.autograd.Function):
             dtab = torch.empty((R, N), device=dy.device, dtype=torch.float32)
             _lib.check(L.grappa_row_gather_bwd(R, N, _p(dr1c), N, plan.ptr(names[1]), plan.ptr(names[2]), _p(dtab), N, _stream()))
             dr1 = dtab
-        return (dx, dw, db, dr1, dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None, None, None, None)
+        if ctx.res1_grad_to is not None and dr1 is not None and ctx.res1_gather is None:
+            ctx.res1_grad_to.value = dr1          # consumed by the first layer's dX GEMM (runs next in this backward pass)
+            dr1 = None
+        return (dx, dw, db, dr1, dr if (has_r2 and ctx.needs_input_grad[4]) else None, None, None, None, None, None, None, None, None)
+
+
+class _GradHolder:
+    __slots__ = ("value",)
+
+    def __init__(self):
+        self.value = None
 
 
 def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0, x_is_elu_out=False,
-           grad_is_preact=False, res1_gather=None):
-    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact, res1_gather)
+           grad_is_preact=False, res1_gather=None, dx_add=None, res1_grad_to=None):
+    return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact, res1_gather,
+                          dx_add, res1_grad_to)
 
 
 def elu_mlp(x, w1, b1, w2, b2, act2=ACT_NONE, res1=None, res2=None, drop_p=0.0):
     """Linear-ELU-Linear with the hidden tensor's ELU backward fused into the second layer's dX GEMM."""
     fuse = FUSE_ELU_GRAD and torch.is_grad_enabled()
-    z = linear(x, w1, b1, act=ACT_ELU, grad_is_preact=fuse)
-    return linear(z, w2, b2, act=act2, res1=res1, res2=res2, drop_p=drop_p, x_is_elu_out=fuse)
+    # the block's input is also its skip connection: its two gradient contributions are summed inside the first layer's dX GEMM
+    holder = _GradHolder() if (FUSE_SKIP_GRAD and res1 is x and torch.is_grad_enabled() and x.requires_grad) else None
+    z = linear(x, w1, b1, act=ACT_ELU, grad_is_preact=fuse, dx_add=holder)
+    return linear(z, w2, b2, act=act2, res1=res1, res2=res2, drop_p=drop_p, x_is_elu_out=fuse, res1_grad_to=holder)
 
 
 class LayerNormFn(torch.autograd.Function):
