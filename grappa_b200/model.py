@@ -115,9 +115,11 @@ class ResidualAttentionBlock(nn.Module):
         p1 = self.dropout1.p if self.training else 0.0
         p2 = self.dropout2.p if self.training else 0.0
         h = ops.layer_norm(h, self.layer_norm.weight, self.layer_norm.bias)
-        ft = ops.linear(h, self.graph_module.fc.weight)
+        # h feeds fc and the skip of head_reducer: the skip's gradient is added in fc's dX GEMM epilogue (ops.LinearFn)
+        holder = ops.skip_grad_holder(h)
+        ft = ops.linear(h, self.graph_module.fc.weight, dx_add=holder)
         att = ops.gnn_attention(ft, plan, self.num_heads)
-        h = ops.linear(att, self.head_reducer.weight, self.head_reducer.bias, res1=h, drop_p=p1)
+        h = ops.linear(att, self.head_reducer.weight, self.head_reducer.bias, res1=h, drop_p=p1, res1_grad_to=holder)
         h = ops.layer_norm(h, self.interaction_norm.weight, self.interaction_norm.bias)
         lin1, lin2 = self.self_interaction[0], self.self_interaction[2]
         return ops.elu_mlp(h, lin1.weight, lin1.bias, lin2.weight, lin2.bias, act2=ops.ACT_ELU, res1=h, drop_p=p2)

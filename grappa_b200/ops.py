@@ -447,6 +447,11 @@ class _GradHolder:
         self.value = None
 
 
+def skip_grad_holder(x):
+    """A holder for the gradient of a skip connection that starts at x, or None when the fusion does not apply."""
+    return _GradHolder() if (FUSE_SKIP_GRAD and torch.is_grad_enabled() and x.requires_grad) else None
+
+
 def linear(x, weight, bias=None, act=ACT_NONE, res1=None, res2=None, drop_p=0.0, out_ld=0, x_is_elu_out=False,
            grad_is_preact=False, res1_gather=None, dx_add=None, res1_grad_to=None):
     return LinearFn.apply(x, weight, bias, res1, res2, act, drop_p, out_ld, x_is_elu_out, grad_is_preact, res1_gather,
@@ -457,7 +462,7 @@ def elu_mlp(x, w1, b1, w2, b2, act2=ACT_NONE, res1=None, res2=None, drop_p=0.0):
     """Linear-ELU-Linear with the hidden tensor's ELU backward fused into the second layer's dX GEMM."""
     fuse = FUSE_ELU_GRAD and torch.is_grad_enabled()
     # the block's input is also its skip connection: its two gradient contributions are summed inside the first layer's dX GEMM
-    holder = _GradHolder() if (FUSE_SKIP_GRAD and res1 is x and torch.is_grad_enabled() and x.requires_grad) else None
+    holder = skip_grad_holder(x) if res1 is x else None
     z = linear(x, w1, b1, act=ACT_ELU, grad_is_preact=fuse, dx_add=holder)
     return linear(z, w2, b2, act=act2, res1=res1, res2=res2, drop_p=drop_p, x_is_elu_out=fuse, res1_grad_to=holder)
 
