@@ -461,7 +461,8 @@ def dp_check(ts, world, rank, dev):
     from grappa_b200.train_step import TrainStep
     dist = torch.distributed
     ts.synchronize()
-    out = {}
+    ts.gather_optimizer_state()            # the fused NVSwitch exchange shards the Adam moments over the ranks
+    out = {"exchange": "nvswitch multimem, fused with AdamW (grappa_dp_exchange_adamw)" if ts._switch is not None else "nccl all-reduce"}
     for name, t in (("params", ts.flat.params), ("exp_avg_sq", ts.flat.exp_avg_sq)):
         bits = t.view(torch.int32).to(torch.int64)
         mine = torch.stack([bits.sum(), (bits * (torch.arange(bits.numel(), device=dev) % 8191 + 1)).sum()])
@@ -473,7 +474,7 @@ def dp_check(ts, world, rank, dev):
     for m in model.modules():
         if isinstance(m, torch.nn.Dropout):
             m.p = 0.0
-    t2 = TrainStep(model, dev, world_size=world, use_cuda_graph=False)
+    t2 = TrainStep(model, dev, world_size=world, use_cuda_graph=False, switch_exchange=False)
     loss_local = t2.compute_gradients(PackedBatch(build_batch(MOLS_PER_RANK * rank), pin=False))
     g_dp = t2.flat.grads.clone()
     dist.all_reduce(g_dp)

@@ -67,6 +67,8 @@ PROTOTYPES = {
     "grappa_collate_float": (I, [I64, P, P, P, P, P]),
     "grappa_molwise_loss": (I, [I64, I64, P, P, P, P, P, P, P, P, P, I, P, I, F, F, F, F, P, P, P, P, P, P, P, P]),
     "grappa_adamw": (I, [I64, P, P, P, P, F, F, F, F, F, I64, F, P]),
+    "grappa_dp_shard": (I, [I64, I64, I, I, P, P]),
+    "grappa_dp_exchange_adamw": (I, [I64, I64, I, I, P, P, P, P, P, P, I64, I64, I, F, F, F, F, F, I64, F, F, P]),
 }
 
 _lib = None

@@ -5,7 +5,7 @@ import sys
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libgrappa_b200.so")
-SOURCES = ["api.cu", "energy.cu", "gemm.cu", "gemm_tc.cu", "gemm_skinny.cu", "elementwise.cu", "gnn_attn.cu", "readout.cu", "loss.cu", "tuples.cu", "collate.cu", "plan.cu"]
+SOURCES = ["api.cu", "energy.cu", "gemm.cu", "gemm_tc.cu", "gemm_skinny.cu", "elementwise.cu", "gnn_attn.cu", "readout.cu", "loss.cu", "tuples.cu", "collate.cu", "plan.cu", "dp_exchange.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 

@@ -42,3 +42,67 @@ def all_reduce_sum_(flat: torch.Tensor, world: int, group=None) -> float:
     if world > 1:
         torch.distributed.all_reduce(flat, op=torch.distributed.ReduceOp.SUM, group=group)
     return 1.0 / world
+
+
+def shard_of(lo: int, hi: int, rank: int, world: int) -> Tuple[int, int]:
+    """Elements [first, first + count) of the flat range [lo, hi) that `rank` owns in the fused exchange + AdamW kernel
+    (csrc/dp_exchange.cu, grappa_dp_shard): equal shares in units of 4 elements, so every shard stays 16-byte aligned."""
+    if lo % 4 or (hi - lo) % 4:
+        raise ValueError("the range must be a multiple of 4 elements")
+    t4 = (hi - lo) // 4
+    a, b = t4 * rank // world, t4 * (rank + 1) // world
+    return lo + 4 * a, 4 * (b - a)
+
+
+class SwitchMemory:
+    """Flat buffers in NVSwitch symmetric memory: every rank allocates the same sizes, the driver maps all of them into
+    one multicast address per buffer (a store to it lands in every rank's copy, a `multimem.ld_reduce` from it returns
+    the sum over the copies, added in the switch).  torch.distributed's symmetric-memory allocator does the rendezvous;
+    the kernels that use the addresses are ours (csrc/dp_exchange.cu).
+
+    `available()` is False on one GPU, without NVSwitch multicast support, or when GRAPPA_DP_SWITCH=0: the training
+    driver then exchanges gradients with NCCL all-reduces."""
+
+    PAD_WORDS = 16384
+
+    def __init__(self, device, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self._symm = symm
+        self.device = device
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world = dist.get_world_size(self.group)
+        self._handles = []
+        pad = symm.empty(self.PAD_WORDS, dtype=torch.int32, device=device)
+        pad.zero_()
+        h = symm.rendezvous(pad, self.group)
+        self._handles.append((pad, h))
+        self.pad = pad
+        self.pad_ptrs = [int(p) for p in h.buffer_ptrs]
+        self.multicast = int(h.multicast_ptr) != 0
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)                  # every rank's flags are zero before anyone raises one
+
+    @staticmethod
+    def available(world: int) -> bool:
+        import os
+        if world <= 1 or os.environ.get("GRAPPA_DP_SWITCH", "1") == "0" or not torch.cuda.is_available():
+            return False
+        try:
+            import importlib
+            importlib.import_module("torch.distributed._symmetric_memory")
+        except Exception:
+            return False
+        return True
+
+    def zeros(self, numel: int):
+        """(local tensor, multicast address) of a zero-filled fp32 buffer that exists on every rank."""
+        t = self._symm.empty(numel, dtype=torch.float32, device=self.device)
+        t.zero_()
+        h = self._symm.rendezvous(t, self.group)
+        self._handles.append((t, h))
+        mc = int(h.multicast_ptr)
+        if mc == 0:
+            raise RuntimeError("no NVSwitch multicast mapping for this allocation")
+        return t, mc

@@ -110,8 +110,8 @@ class ResidualAttentionBlock(nn.Module):
         self.self_interaction = nn.Sequential(nn.Linear(out_feats, 4 * out_feats), self.activation,
                                               nn.Linear(4 * out_feats, out_feats), self.activation)
 
-    def forward(self, plan, h):
-        """graph_attention.py:289-323."""
+    def forward(self, plan, h, pre_ffn=None):
+        """graph_attention.py:289-323.  `pre_ffn` is called right before the self-interaction weights are first read."""
         p1 = self.dropout1.p if self.training else 0.0
         p2 = self.dropout2.p if self.training else 0.0
         h = ops.layer_norm(h, self.layer_norm.weight, self.layer_norm.bias)
@@ -122,6 +122,8 @@ class ResidualAttentionBlock(nn.Module):
         h = ops.linear(att, self.head_reducer.weight, self.head_reducer.bias, res1=h, drop_p=p1, res1_grad_to=holder)
         h = ops.layer_norm(h, self.interaction_norm.weight, self.interaction_norm.bias)
         lin1, lin2 = self.self_interaction[0], self.self_interaction[2]
+        if pre_ffn is not None:
+            pre_ffn()
         return ops.elu_mlp(h, lin1.weight, lin1.bias, lin2.weight, lin2.bias, act2=ops.ACT_ELU, res1=h, drop_p=p2)
 
 
@@ -202,12 +204,15 @@ class GrappaGNN(nn.Module):
         lin = self.pre_dense[0]
         p0 = self.initial_dropout.p if self.training else 0.0
         h = ops.linear(x, lin.weight, lin.bias, act=ops.ACT_ELU, drop_p=p0)
-        hook = getattr(self, "stage_hook", None)     # training driver: called before block i >= 1 reads its parameters
+        # training driver: hook(i, 0) before block i reads its attention parameters, hook(i, 1) before its self-interaction
+        hook = getattr(self, "stage_hook", None)
         if not self.no_convs:
             for i, block in enumerate(self.blocks):
-                if hook is not None and i >= 1:
-                    hook(i)
-                h = block(plan, h)
+                if hook is not None:
+                    hook(i, 0)
+                    h = block(plan, h, pre_ffn=lambda i=i: hook(i, 1))
+                else:
+                    h = block(plan, h)
         lin = self.post_dense[0]
         pf = self.final_dropout.p if self.training else 0.0
         h = ops.linear(h, lin.weight, lin.bias, drop_p=pf)

@@ -13,13 +13,15 @@ B200-first design choices
 Molecules are independent units: rank r owns a contiguous slice of the global batch, no data-path collective exists
 other than the gradient all-reduce.
 """
+import ctypes as _ctypes
+import os as _os
 from typing import Dict, Optional
 
 import torch
 
 from . import _lib, ops
 from .batching import DeviceBatch, PackedBatch
-from .dp import all_reduce_sum_
+from .dp import SwitchMemory, all_reduce_sum_, shard_of
 from .energy import Energy
 from .plan import get_plan
 
@@ -53,7 +55,7 @@ class _LossHandle:
 
 
 class FlatParameters:
-    def __init__(self, model: torch.nn.Module, device):
+    def __init__(self, model: torch.nn.Module, device, switch=None):
         self.named = [(n, p) for n, p in model.named_parameters() if p.requires_grad and not any(u in n for u in _UNUSED)]
         self.offsets: Dict[str, int] = {}
         total = 0
@@ -61,8 +63,13 @@ class FlatParameters:
             self.offsets[n] = total
             total += (p.numel() + 3) // 4 * 4            # 16-byte aligned views (vectorised GEMM loads)
         self.numel = total
-        self.params = torch.zeros(total, device=device, dtype=torch.float32)
-        self.grads = torch.zeros(total, device=device, dtype=torch.float32)
+        self.params_mc = self.grads_mc = 0
+        if switch is not None:          # NVSwitch symmetric memory: the fused exchange + AdamW kernel addresses all ranks' copies
+            self.params, self.params_mc = switch.zeros(total)
+            self.grads, self.grads_mc = switch.zeros(total)
+        else:
+            self.params = torch.zeros(total, device=device, dtype=torch.float32)
+            self.grads = torch.zeros(total, device=device, dtype=torch.float32)
         self.exp_avg = torch.zeros(total, device=device, dtype=torch.float32)
         self.exp_avg_sq = torch.zeros(total, device=device, dtype=torch.float32)
         self.params_lo = torch.zeros(total, device=device, dtype=torch.float32)     # lo planes of the pre-split weights
@@ -86,7 +93,8 @@ class TrainStep:
                  energy_weight: float = 1.0, gradient_weight: float = 0.8, proper_regularisation: float = 1.0,
                  improper_regularisation: float = 1.0, world_size: int = 1, use_cuda_graph: bool = True,
                  process_group=None, overlap_comm: Optional[bool] = None, split_update: Optional[bool] = None,
-                 max_cached_shapes: int = 8, warmup_steps: int = 0):
+                 max_cached_shapes: int = 8, warmup_steps: int = 0, ffn_split_blocks=(0,),
+                 switch_exchange: Optional[bool] = None):
         """`warmup_steps`: linear learning-rate warm-up from 0 to `lr` over that many steps, as
         training/lightning_model.py:136-161 (`_get_lr`; the reference's config uses 500; call `restart_warmup()` where
         the reference re-arms it at a restart epoch, :199-201).  0 (default) = constant lr, which is what bench.py
@@ -96,7 +104,26 @@ class TrainStep:
         self._warmup_step = 0 if self.warmup_steps > 0 else None
         self.model = model.to(self.device).train()
         self.energy = Energy(terms=["bond", "angle", "proper", "improper"], materialize_tuple_terms=False)
-        self.flat = FlatParameters(self.model, self.device)
+        # Gradient exchange for world_size > 1: on an NVSwitch domain with multicast memory the flat parameter and gradient
+        # buffers live in symmetric memory and every parameter stage is exchanged AND updated by one kernel of ours
+        # (grappa_dp_exchange_adamw: in-switch gradient sum -> AdamW on this rank's shard -> multicast store of the new
+        # parameters; optimiser state sharded over the ranks, see gather_optimizer_state).  Otherwise: NCCL all-reduce per
+        # stage + AdamW on every rank.
+        self._switch = None
+        self.pg = process_group
+        if world_size > 1 and (switch_exchange is None or switch_exchange) and SwitchMemory.available(world_size):
+            try:
+                sw = SwitchMemory(self.device, process_group)
+                self._switch = sw if sw.multicast else None
+            except Exception as e:          # no multicast support on this box / driver: the NCCL path is complete on its own
+                if switch_exchange:
+                    raise
+                import warnings
+                warnings.warn(f"NVSwitch symmetric memory is not available ({str(e)[:200]}); gradients go through NCCL all-reduce")
+        self._slot_of = {}
+        self._dp_ctas = int(_os.environ.get("GRAPPA_DP_CTAS", "32"))
+        self._dp_spin_seconds = float(_os.environ.get("GRAPPA_DP_SPIN_SECONDS", "120"))
+        self.flat = FlatParameters(self.model, self.device, switch=self._switch)
         if ops.USE_WEIGHT_LO:                                   # lo planes of the initial weights (refreshed after every AdamW)
             _lib.check(_lib.lib().grappa_split_lo(self.flat.numel, ops._p(self.flat.params), ops._p(self.flat.params_lo),
                                                   ops._stream()))
@@ -153,24 +180,30 @@ class TrainStep:
         first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
         self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
         assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
-        # Staged update (world_size > 1): the parameters are exchanged + updated in FORWARD order in five stages --
+        # Staged update (world_size > 1): the parameters are exchanged + updated in FORWARD order in stages --
         # [pre_dense + GNN block 0 | block 1 | block 2 | block 3 + post_dense | the four writers].  Stage 0 runs on the compute
-        # stream; stages 1..4 (all-reduce wait + AdamW + plane refresh) on the update stream UNDER the next step's forward,
+        # stream; the later ones (all-reduce wait + AdamW + plane refresh) on the update stream UNDER the next step's forward,
         # which waits for stage i only right before it reads that stage's parameters (external-event wait nodes in the
-        # step graph).  Exposed communication = the first stage's all-reduce (1/8 of the gradient bytes).
+        # step graph).  Exposed communication = the first stage's all-reduce.
+        # The block listed in `ffn_split_blocks` (default: block 0) is cut once more in front of its self-interaction
+        # weights (4/5 of a block's parameters), so the one all-reduce nothing can hide -- the first stage's, which the next
+        # forward needs at once -- carries pre_dense + the attention half of block 0 only (2.3 MB instead of 10.7 MB).
         bounds = [0]
         n_blocks = len(getattr(self.model.gnn, "blocks", []))
-        for i in range(1, n_blocks):
-            first = [self.flat.offsets[n] for n, _ in self.flat.named if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}.")]
-            if first:
-                bounds.append(min(first))
-        bounds += [self.bucket_split, self.flat.numel]
+        self._stage_mark = {}                       # (block, part) -> first flat offset of that stage
+        for i in range(n_blocks):
+            own = sorted((self.flat.offsets[n], n) for n, _ in self.flat.named
+                         if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}."))
+            if not own:
+                continue
+            if i >= 1:
+                self._stage_mark[(i, 0)] = own[0][0]
+            ffn = [o for o, n in own if ".self_interaction." in n]
+            if i in ffn_split_blocks and ffn and all(".self_interaction." in n for o, n in own if o >= min(ffn)):
+                self._stage_mark[(i, 1)] = min(ffn)
+        bounds += list(self._stage_mark.values()) + [self.bucket_split, self.flat.numel]
         self._stage_bounds = sorted(set(bounds))
-        self._stage_of_block = {}
-        for i in range(1, n_blocks):
-            first = [self.flat.offsets[n] for n, _ in self.flat.named if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}.")]
-            if first:
-                self._stage_of_block[i] = self._stage_bounds.index(min(first))
+        self._stage_of_mark = {k: self._stage_bounds.index(o) for k, o in self._stage_mark.items()}
         self._writer_stage = self._stage_bounds.index(self.bucket_split) if self.bucket_split in self._stage_bounds[:-1] else None
         for _ in range(len(self._stage_bounds) - 1):
             ev = torch.cuda.Event(external=True)
@@ -210,7 +243,8 @@ class TrainStep:
             elif self.split_update:
                 plan = get_plan(g)
                 cur = torch.cuda.current_stream(self.device)
-                self.model.gnn.stage_hook = lambda i: self._stage_ready[self._stage_of_block[i]].wait(cur) if i in self._stage_of_block else None
+                self.model.gnn.stage_hook = lambda i, part: (self._stage_ready[self._stage_of_mark[(i, part)]].wait(cur)
+                                                             if (i, part) in self._stage_of_mark else None)
                 try:
                     g = self.model.gnn(g, plan)
                 finally:
@@ -352,7 +386,7 @@ class TrainStep:
         return st["loss"]
 
     def all_reduce_gradients(self):
-        if self.overlap_comm:            # already exchanged inside compute_gradients (two buckets)
+        if self.overlap_comm or self._switch is not None:     # exchanged inside compute_gradients / by the update kernel itself
             self._grad_scale = 1.0 / self.world_size
             return
         self._grad_scale = all_reduce_sum_(self.flat.grads, self.world_size, self.pg)
@@ -408,9 +442,20 @@ class TrainStep:
         if hi <= lo:
             return
         ptr = lambda t: t.data_ptr() + 4 * lo
-        _lib.check(_lib.lib().grappa_adamw(hi - lo, ptr(f.params), ptr(f.grads), ptr(f.exp_avg), ptr(f.exp_avg_sq),
-                                           self._lr_now, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
-                                           getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
+        if self._switch is not None:       # exchange + update in one kernel; launches that may overlap use different flag slots
+            sw = self._switch
+            n_ctas = max(1, min(self._dp_ctas, (shard_of(lo, hi, 0, sw.world)[1] // 4 + 2047) // 2048))
+            slot = self._slot_of.setdefault((lo, hi), len(self._slot_of))
+            pads = (_ctypes.c_uint64 * sw.world)(*sw.pad_ptrs)
+            _lib.check(_lib.lib().grappa_dp_exchange_adamw(lo, hi, sw.rank, sw.world, f.grads_mc, f.params_mc, f.params.data_ptr(),
+                                                           f.exp_avg.data_ptr(), f.exp_avg_sq.data_ptr(), pads, sw.PAD_WORDS,
+                                                           slot * self._dp_ctas * sw.world, n_ctas, self._lr_now, self.betas[0],
+                                                           self.betas[1], self.eps, self.wd, self.t, 1.0 / self.world_size,
+                                                           self._dp_spin_seconds, ops._stream()))
+        else:
+            _lib.check(_lib.lib().grappa_adamw(hi - lo, ptr(f.params), ptr(f.grads), ptr(f.exp_avg), ptr(f.exp_avg_sq),
+                                               self._lr_now, self.betas[0], self.betas[1], self.eps, self.wd, self.t,
+                                               getattr(self, "_grad_scale", 1.0 / self.world_size), ops._stream()))
         ops.WEIGHT_EPOCH[0] += 1         # invalidates lo planes cached for use outside this driver
         if self._planes is not None:     # bf16 planes of the updated weights for the next step's forward / dX GEMMs
             self._refresh_planes(lo, hi)
@@ -428,7 +473,7 @@ class TrainStep:
         cur = torch.cuda.current_stream(self.device)
         b = self._stage_bounds
         works = [None] * (len(b) - 1)
-        if self.world_size > 1:
+        if self.world_size > 1 and self._switch is None:
             for i in range(len(b) - 1):                            # issued in forward order: NCCL completes them in that order
                 works[i] = dist.all_reduce(self.flat.grads[b[i]:b[i + 1]], op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
         self._grad_scale = 1.0 / self.world_size
@@ -445,6 +490,23 @@ class TrainStep:
                     works[i].wait()
                 self._adamw_range(b[i], b[i + 1])
                 self._stage_ready[i].record(self._upd_stream)
+
+    def gather_optimizer_state(self):
+        """With the fused NVSwitch exchange every rank updates only its shard of exp_avg / exp_avg_sq; this completes all
+        ranks' copies (call before writing a checkpoint or comparing optimiser state across ranks)."""
+        if self._switch is None:
+            return
+        dist = torch.distributed
+        self.synchronize()
+        sw = self._switch
+        for (lo, hi) in self._slot_of:
+            for r in range(sw.world):
+                first, count = shard_of(lo, hi, r, sw.world)
+                if count:
+                    src = dist.get_global_rank(sw.group, r)
+                    dist.broadcast(self.flat.exp_avg[first:first + count], src=src, group=sw.group)
+                    dist.broadcast(self.flat.exp_avg_sq[first:first + count], src=src, group=sw.group)
+        torch.cuda.synchronize(self.device)
 
     def synchronize(self):
         """All parameter updates issued so far have completed on the device."""

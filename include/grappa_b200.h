@@ -367,6 +367,26 @@ int grappa_adamw(int64_t n, float* param, const float* grad, float* exp_avg, flo
                  float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
                  void* stream);
 
+/* Data-parallel training on one NVSwitch domain: gradient exchange FUSED with AdamW, one launch per parameter stage
+ * (replaces the NCCL all-reduce of Lightning's DDP strategy followed by torch.optim.AdamW on every rank,
+ * training/lightning_model.py:368-370; csrc/dp_exchange.cu).  Flat element range [lo, hi) (multiples of 4) is cut in
+ * `world` shards (grappa_dp_shard); this rank reads ITS shard's gradients summed over all ranks by the switch
+ * (multimem.ld_reduce on grads_mc), updates the shard with its own exp_avg / exp_avg_sq (the optimiser state is sharded:
+ * only the owner's part of those buffers is meaningful), and stores the new parameters to every rank through
+ * params_mc (multimem.st).  grads_mc / params_mc: MULTICAST addresses of the flat gradient / parameter buffers
+ * (element 0); params / exp_avg / exp_avg_sq: this rank's local buffers (element 0).  peer_signal_pads: HOST array of
+ * `world` device addresses, entry r = rank r's signal pad (pad_words zero-initialised uint32, in peer-mapped memory);
+ * the launch uses the words [slot_base, slot_base + n_ctas*world) of every pad, which launches that may overlap in
+ * time must not share.  Every rank must make the same call (same range, n_ctas, slot_base) in the same order.
+ * A peer that does not arrive within spin_seconds (0 = wait forever) makes the kernel trap.  step >= 1 as in
+ * grappa_adamw; grad_scale = 1/world for a mean over ranks. */
+int grappa_dp_shard(int64_t lo, int64_t hi, int rank, int world, int64_t* first_out, int64_t* count_out);
+int grappa_dp_exchange_adamw(int64_t lo, int64_t hi, int rank, int world, const float* grads_mc, float* params_mc,
+                             float* params, float* exp_avg, float* exp_avg_sq, const uint64_t* peer_signal_pads,
+                             int64_t pad_words, int64_t slot_base, int n_ctas, float lr, float beta1, float beta2,
+                             float eps, float weight_decay, int64_t step, float grad_scale, float spin_seconds,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif
