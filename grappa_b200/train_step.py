@@ -121,7 +121,10 @@ class TrainStep:
                 import warnings
                 warnings.warn(f"NVSwitch symmetric memory is not available ({str(e)[:200]}); gradients go through NCCL all-reduce")
         self._slot_of = {}
-        self._dp_ctas = int(_os.environ.get("GRAPPA_DP_CTAS", "32"))
+        # CTAs of the exchange kernel (it runs under the next forward: enough loads in flight for the links, few enough SMs
+        # taken from the forward).  Measured on the cfg-2 step: 2 GPUs 16/32/64 CTAs -> 3.32/3.26/3.30 ms, 8 GPUs
+        # 16/32/64 -> 3.25/3.30/3.31 ms (shards shrink with the world size).
+        self._dp_ctas = int(_os.environ.get("GRAPPA_DP_CTAS", str(max(8, min(32, 128 // max(world_size, 1))))))
         self._dp_spin_seconds = float(_os.environ.get("GRAPPA_DP_SPIN_SECONDS", "120"))
         self.flat = FlatParameters(self.model, self.device, switch=self._switch)
         if ops.USE_WEIGHT_LO:                                   # lo planes of the initial weights (refreshed after every AdamW)
