@@ -326,6 +326,10 @@ def main():
         line["clocks"] = clocks.summary(t_clock0, t_clock1)
         line["clocks"]["window"] = "device-resident + both end-to-end timed regions (back to back, all under load)"
     if world > 1:
+        line["config"]["gradient_exchange"] = ("grappa_dp_exchange_adamw: in-switch gradient sum (multimem.ld_reduce) + AdamW on the "
+                                               "owner's shard + multicast store of the parameters, one kernel per stage, stages "
+                                               "after the first under the next forward" if ts._switch is not None else
+                                               "NCCL all-reduce per stage + AdamW on every rank, stages after the first under the next forward")
         line["dp_check"] = dp_check(ts, world, rank, dev)
     line["strong_scaling_global256"] = strong_scaling(ts, world, rank, dev, K)
 
@@ -335,6 +339,9 @@ def main():
         _lib.PROFILE_HINTS.update(n_edges=g_host.num_edges(), n_atoms=g_host.num_nodes("n1"))
         ts_graph = ts.use_cuda_graph
         ts.use_cuda_graph = False
+        # this pass runs on rank 0 ALONE: the update must not wait for the other ranks, so it is the local AdamW kernel
+        # (at N > 1 the timed steps use grappa_dp_exchange_adamw instead, which needs every rank)
+        ts_switch, ts._switch = ts._switch, None
         for _ in range(2):
             ts.compute_gradients(packed, load=False)
         prof = _lib.Profiler()
@@ -344,6 +351,7 @@ def main():
         summ = prof.summary()                          # call counts and algorithmic work per entry point
         _lib.profiler = None
         ts.use_cuda_graph = ts_graph
+        ts._switch = ts_switch
         # device time per entry point: its recorded launches replayed back to back in one CUDA graph (CUDA events)
         gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"}     # one kernel family: one roofline entry
         summ.setdefault("grappa_gemm", {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
