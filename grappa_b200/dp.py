@@ -54,6 +54,21 @@ def shard_of(lo: int, hi: int, rank: int, world: int) -> Tuple[int, int]:
     return lo + 4 * a, 4 * (b - a)
 
 
+def gather_shards_(tensors, ranges, group=None) -> None:
+    """Completes every rank's copy of flat buffers whose ranges are sharded as `shard_of` says (the Adam moments under the
+    fused exchange): each owner broadcasts its shard of every range.  In place; any backend."""
+    dist = torch.distributed
+    group = group if group is not None else dist.group.WORLD
+    world = dist.get_world_size(group)
+    for (lo, hi) in ranges:
+        for r in range(world):
+            first, count = shard_of(lo, hi, r, world)
+            if count:
+                src = dist.get_global_rank(group, r)
+                for t in tensors:
+                    dist.broadcast(t[first:first + count], src=src, group=group)
+
+
 class SwitchMemory:
     """Flat buffers in NVSwitch symmetric memory: every rank allocates the same sizes, the driver maps all of them into
     one multicast address per buffer (a store to it lands in every rank's copy, a `multimem.ld_reduce` from it returns

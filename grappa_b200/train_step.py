@@ -21,7 +21,7 @@ import torch
 
 from . import _lib, ops
 from .batching import DeviceBatch, PackedBatch
-from .dp import SwitchMemory, all_reduce_sum_, shard_of
+from .dp import SwitchMemory, all_reduce_sum_, gather_shards_, shard_of
 from .energy import Energy
 from .plan import get_plan
 
@@ -499,16 +499,8 @@ class TrainStep:
         ranks' copies (call before writing a checkpoint or comparing optimiser state across ranks)."""
         if self._switch is None:
             return
-        dist = torch.distributed
         self.synchronize()
-        sw = self._switch
-        for (lo, hi) in self._slot_of:
-            for r in range(sw.world):
-                first, count = shard_of(lo, hi, r, sw.world)
-                if count:
-                    src = dist.get_global_rank(sw.group, r)
-                    dist.broadcast(self.flat.exp_avg[first:first + count], src=src, group=sw.group)
-                    dist.broadcast(self.flat.exp_avg_sq[first:first + count], src=src, group=sw.group)
+        gather_shards_((self.flat.exp_avg, self.flat.exp_avg_sq), list(self._slot_of), self._switch.group)
         torch.cuda.synchronize(self.device)
 
     def synchronize(self):

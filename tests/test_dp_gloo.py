@@ -81,3 +81,82 @@ def test_two_rank_gradient_allreduce_matches_global_batch(tmp_path):
     worst, loss = np.load(os.path.join(str(tmp_path), "worst.npy"))
     assert np.isfinite(loss)
     assert worst < 2e-4, f"data-parallel mean gradient deviates from the global-batch gradient by {worst:.2e} (relative to max)"
+
+
+# ---- the sharded exchange + update of csrc/dp_exchange.cu, its host-side logic (owner ranges, state gather) ----
+
+def test_owner_shards_tile_every_range_and_match_the_library():
+    import ctypes
+    from grappa_b200 import _lib
+    from grappa_b200.dp import shard_of
+    L = _lib.lib()
+    for lo, hi in ((0, 0), (0, 4), (8, 20), (40, 20836868 // 4 * 4), (569856, 2669568)):
+        for world in (1, 2, 3, 4, 8, 16):
+            nxt = lo
+            for r in range(world):
+                first, count = shard_of(lo, hi, r, world)
+                assert first == nxt and first % 4 == 0 and count % 4 == 0 and count >= 0
+                nxt = first + count
+                a, b = ctypes.c_int64(-1), ctypes.c_int64(-1)
+                assert L.grappa_dp_shard(lo, hi, r, world, ctypes.byref(a), ctypes.byref(b)) == 0
+                assert (a.value, b.value) == (first, count)
+            assert nxt == hi
+    with pytest.raises(ValueError):
+        shard_of(2, 10, 0, 2)
+    a, b = ctypes.c_int64(), ctypes.c_int64()
+    assert L.grappa_dp_shard(2, 10, 0, 2, ctypes.byref(a), ctypes.byref(b)) != 0
+
+
+def _adamw_(p, g, m, v, step, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8, wd=0.01, gscale=1.0):
+    """The arithmetic of adamw_elem (csrc/dp_exchange.cu) / adamw_kernel on tensors, in place."""
+    g = g * gscale
+    bc1, bc2s = 1.0 - b1 ** step, (1.0 - b2 ** step) ** 0.5
+    pi = p * (1.0 - lr * wd)
+    m.mul_(b1).add_((1.0 - b1) * g)
+    v.mul_(b2).add_((1.0 - b2) * g * g)
+    p.copy_(pi - (lr / bc1) * (m / (v.sqrt() / bc2s + eps)))
+
+
+def _shard_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from grappa_b200.dp import gather_shards_, shard_of
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        n = 4 * 61
+        ranges = [(0, 40), (40, 44), (44, n)]
+        torch.manual_seed(0)
+        p_rep = torch.randn(n)
+        p_sh = p_rep.clone()
+        m_rep, v_rep, m_sh, v_sh = (torch.zeros(n) for _ in range(4))
+        for step in range(1, 4):
+            torch.manual_seed(100 * step + rank)
+            g = torch.randn(n)
+            total = g.clone()
+            dist.all_reduce(total)                                # what every rank would hold after an all-reduce
+            _adamw_(p_rep, total, m_rep, v_rep, step, gscale=1.0 / world)       # replicated: AdamW on everything, on every rank
+            for lo, hi in ranges:                                # sharded: the owner updates its elements and sends the parameters
+                first, count = shard_of(lo, hi, rank, world)
+                sl = slice(first, first + count)
+                _adamw_(p_sh[sl], total[sl], m_sh[sl], v_sh[sl], step, gscale=1.0 / world)
+                for r in range(world):
+                    f, c = shard_of(lo, hi, r, world)
+                    if c:
+                        dist.broadcast(p_sh[f:f + c], src=r)
+            assert torch.equal(p_sh, p_rep), f"step {step}: sharded update differs from the replicated one"
+        own = torch.zeros(n, dtype=torch.bool)
+        for lo, hi in ranges:
+            first, count = shard_of(lo, hi, rank, world)
+            own[first:first + count] = True
+        assert torch.equal(m_sh[own], m_rep[own]) and not torch.equal(m_sh, m_rep)      # only the owner's part is current
+        gather_shards_((m_sh, v_sh), ranges)
+        assert torch.equal(m_sh, m_rep) and torch.equal(v_sh, v_rep)
+        open(os.path.join(out_dir, f"ok{rank}"), "w").close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_update_equals_replicated_update_world2(tmp_path):
+    port = _free_port()
+    mp.spawn(_shard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    assert sorted(os.listdir(tmp_path)) == ["ok0", "ok1"]
