@@ -1,17 +1,20 @@
 """
 Data-parallel training-step driver.  Replaces, for benchmarking and as the minimal trainer, the
 Lightning orchestration of training/lightning_model.py:228-254,368-370: forward (GrappaModel -> Energy), molecule-wise
-loss, backward, gradient all-reduce over NCCL (one process per GPU), AdamW.
+loss, backward, gradient exchange between the ranks (one process per GPU), AdamW.
 
 B200-first design choices
   - parameters live in ONE flat fp32 buffer and their gradients in another: the backward GEMMs write weight
-    gradients straight into the flat gradient buffer (ops.GRAD_SINK), the all-reduce is a single NCCL call over
-    83 MB, AdamW is a single kernel launch;
+    gradients straight into the flat gradient buffer (ops.GRAD_SINK), AdamW is one launch per parameter stage;
+  - for world_size > 1 the two flat buffers live in NVSwitch symmetric memory and the gradient exchange is FUSED with
+    AdamW (csrc/dp_exchange.cu: in-switch sum of the owner's shard, update, multicast store of the new parameters),
+    staged in forward order so that all stages but the first run under the next step's forward; NCCL all-reduces in
+    the same staging where multicast memory is not available;
   - inputs arrive as two pinned host buffers (batching.PackedBatch) copied into static device buffers;
   - forward + loss + backward are captured once per batch shape in a CUDA graph and replayed; dropout masks stay
     fresh across replays through a device-side seed that the graph itself increments.
 Molecules are independent units: rank r owns a contiguous slice of the global batch, no data-path collective exists
-other than the gradient all-reduce.
+other than the gradient exchange.
 """
 import ctypes as _ctypes
 import os as _os
@@ -466,8 +469,8 @@ class TrainStep:
             _lib.check(_lib.lib().grappa_split_lo(hi - lo, ptr(f.params), ptr(f.params_lo), ops._stream()))
 
     def exchange_and_update(self):
-        """Gradient exchange + AdamW.  With `split_update` the GNN bucket goes first on the compute stream and the
-        writers' bucket (all-reduce + AdamW) runs on the update stream while the next step's GNN forward is computing."""
+        """Gradient exchange + AdamW.  With `split_update` the first parameter stage goes on the compute stream and the later
+        ones (exchange + AdamW + plane refresh) on the update stream while the next step's forward is computing."""
         if not self.split_update or self.overlap_comm or self.bucket_split in (0, self.flat.numel):
             self.all_reduce_gradients()
             self.optimizer_step()
