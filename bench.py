@@ -336,123 +336,132 @@ def main():
     # ---- per-kernel timing with CUDA events (eager pass, rank 0) -> roofline ----
     if rank == 0:
         pk, pk_src = peaks()
-        _lib.PROFILE_HINTS.update(n_edges=g_host.num_edges(), n_atoms=g_host.num_nodes("n1"))
-        ts_graph = ts.use_cuda_graph
-        ts.use_cuda_graph = False
-        # this pass runs on rank 0 ALONE: the update must not wait for the other ranks, so it is the local AdamW kernel
-        # (at N > 1 the timed steps use grappa_dp_exchange_adamw instead, which needs every rank)
-        ts_switch, ts._switch = ts._switch, None
-        for _ in range(2):
-            ts.compute_gradients(packed, load=False)
-        prof = _lib.Profiler()
-        _lib.profiler = prof
-        ts.compute_gradients(packed, load=False)      # ONE step's worth of C-ABI calls, with their arguments
-        ts.optimizer_step()
-        summ = prof.summary()                          # call counts and algorithmic work per entry point
-        _lib.profiler = None
-        ts.use_cuda_graph = ts_graph
-        ts._switch = ts_switch
-        # device time per entry point: its recorded launches replayed back to back in one CUDA graph (CUDA events)
-        gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"}     # one kernel family: one roofline entry
-        summ.setdefault("grappa_gemm", {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
-        for other in ("grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"):
-            if other in summ:
-                extra_g = summ.pop(other)
-                for k2 in ("calls", "ms", "flops"):
-                    summ["grappa_gemm"][k2] += extra_g[k2]
-        names = sorted(summ.keys())
-        dev_ms = {n: prof.replay_ms(gemm_names if n == "grappa_gemm" else {n}) for n in names}
-        tot = sum(dev_ms.values())
-        step_ms = ms / K
-        gm = summ["grappa_gemm"]
-        gemm_ms = dev_ms["grappa_gemm"]
-        tf = gm["flops"] / (gemm_ms * 1e-3) / 1e12
-        peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-        # fp32-accurate ceiling: a split product costs 3 MMAs; kind::f16 (bf16 planes) runs at the bf16 peak, kind::tf32 at
-        # half of it -> time floor = flops_bf16x3 / (peak / 3) + flops_3xtf32 / (peak / 6)
-        _mnk = lambda n, a: (a[0], a[1], a[2]) if n == "grappa_gemm_bf16x3" else (a[1], a[2], a[3])
-        _gflops = lambda keep: (sum(2.0 * _mnk(n, a)[0] * _mnk(n, a)[1] * _mnk(n, a)[2] for n, _, _, a in prof.records
-                                    if n == "grappa_gemm_bf16x3" and keep(n, a)),
-                                sum(2.0 * _mnk(n, a)[0] * _mnk(n, a)[1] * _mnk(n, a)[2] for n, _, _, a in prof.records
-                                    if n in gemm_names and n != "grappa_gemm_bf16x3" and keep(n, a)))
-        def ceiling_frac(keep, t_ms):
-            fb, ft = _gflops(keep)
-            return (fb / (peak_tf / 3.0) + ft / (peak_tf / 6.0)) / 1e12 / (t_ms * 1e-3)
-        every = lambda n, a: True
-        line["roofline"] = {"kernel": {0: "sgemm_kernel", 1: "gemm_tc_kernel", 2: "gemm_bf16_kernel + gemm_tc_kernel"}[ops.MATH_MODE] +
-                                      " (grappa_gemm: all dense layers fwd+bwd, fused bias/ELU/dropout/residual epilogue)",
-                            "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
-                            "frac_of_fp32_accurate_ceiling": ceiling_frac(every, gemm_ms),
-                            "flops_bf16x3": _gflops(every)[0], "flops_3xtf32": _gflops(every)[1],
-                            "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
-                            "pipe": "fp32 FFMA (math_mode 0)" if ops.MATH_MODE == 0 else
-                                    "tcgen05, 3 MMAs per product for fp32-level accuracy: kind::f16 on bf16 hi/lo planes (forward, "
-                                    "dX; ceiling = bf16 peak / 3) and kind::tf32 (weight gradients; ceiling = bf16 peak / 6); "
-                                    "frac_of_fp32_accurate_ceiling = that time floor / measured time",
-                            "share_of_step": gemm_ms / tot, "launches_per_step": gm["calls"],
-                            "share_note": "share of the summed device time of this library's kernels; the step itself overlaps "
-                                          "kernels on parallel streams, so the sum exceeds the step time",
-                            "flops_per_step": gm["flops"], "ms_per_step": gemm_ms,
-                            "avg_launch_us": gemm_ms * 1e3 / gm["calls"],
-                            "method": "the step's recorded launches replayed back to back in a CUDA graph, CUDA events",
-                            "in_step": {"achieved": gm["flops"] / (step_ms * 1e-3) / 1e12,
-                                        "frac": gm["flops"] / (step_ms * 1e-3) / 1e12 / peak_tf,
-                                        "frac_of_fp32_accurate_ceiling": ceiling_frac(every, step_ms),
-                                        "note": "the same flops over the measured step time: inside the step the GEMMs of "
-                                                "five streams overlap each other and the other kernels, so this aggregate "
-                                                "rate is what the step sustains; `achieved` above is the serial replay"}}
-        # The weight-gradient GEMMs are issued on low-priority side streams with a CTA budget (un-split: 4-64 CTAs
-        # each) so that they run UNDER the activation-gradient chains; replayed alone and serially they look slow by
-        # construction.  Both classes are reported; `achieved` above is over all launches, as the contract defines it.
-        is_bg = lambda n, a: n in ("grappa_gemm", "grappa_gemm_ex", "grappa_gemm_bf16x3") and ((a[19] >> 16) & 1) == 1
-        mnk = lambda n, a: (a[0], a[1], a[2]) if n == "grappa_gemm_bf16x3" else (a[1], a[2], a[3])
-        fl = {"foreground": [0.0, 0], "background": [0.0, 0]}
-        for n, _, _, a in prof.records:
-            if n in gemm_names:
-                c = fl["background" if is_bg(n, a) else "foreground"]
-                c[0] += 2.0 * mnk(n, a)[0] * mnk(n, a)[1] * mnk(n, a)[2]
-                c[1] += 1
-        for cls, keep in (("foreground", lambda n, a: not is_bg(n, a)), ("background", is_bg)):
-            ms_c = prof.replay_ms(gemm_names, keep=keep)
-            if ms_c > 0:
-                line["roofline"][cls] = {"launches": fl[cls][1], "flops": fl[cls][0], "ms": ms_c,
-                                         "achieved": fl[cls][0] / (ms_c * 1e-3) / 1e12,
-                                         "frac_of_fp32_accurate_ceiling": ceiling_frac(keep, ms_c)}
-        line["roofline"]["class_note"] = ("foreground = GEMMs on the critical chains (forward, activation gradients); background = "
-                                          "weight-gradient GEMMs on low-priority side streams, deliberately un-split (few CTAs) so "
-                                          "that they fill idle SMs under the chains: 4.06 -> 3.93 ms per step")
-        others = {}
-        for name, label in (("grappa_energy_fwd", "energy_fwd"), ("grappa_energy_vjp", "energy_vjp"), ("grappa_gnn_attn_fwd", "gnn_attn_fwd")):
-            if name in summ and dev_ms.get(name, 0) > 0:
-                d = summ[name]
-                gbs = d["bytes"] / (dev_ms[name] * 1e-3) / 1e9
-                others[label] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
-                                 "us_per_call": dev_ms[name] * 1e3 / d["calls"]}
-        try:     # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/)
-            with open(os.path.join(ROOT, "profiles", "r02_gemm_traffic.json")) as f:
-                tr = json.load(f)
-            line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
-            line["roofline"]["traffic_note"] = tr["note"]
-        except Exception:
-            pass
-        line["roofline_other_kernels"] = others
-        line["kernel_ms_per_step"] = {k: round(v, 4) for k, v in sorted(dev_ms.items(), key=lambda kv: -kv[1])}
-        line["kernel_ms_per_step"]["_sum_own_kernels"] = round(tot, 4)
-        line["kernel_ms_per_step"]["_step"] = round(step_ms, 4)
+        ts_graph, ts_switch = ts.use_cuda_graph, ts._switch
+        try:
+            _lib.PROFILE_HINTS.update(n_edges=g_host.num_edges(), n_atoms=g_host.num_nodes("n1"))
+            ts.use_cuda_graph = False
+            # this pass runs on rank 0 ALONE: the update must not wait for the other ranks, so it is the local AdamW kernel
+            # (at N > 1 the timed steps use grappa_dp_exchange_adamw instead, which needs every rank)
+            ts._switch = None
+            for _ in range(2):
+                ts.compute_gradients(packed, load=False)
+            prof = _lib.Profiler()
+            _lib.profiler = prof
+            ts.compute_gradients(packed, load=False)      # ONE step's worth of C-ABI calls, with their arguments
+            ts.optimizer_step()
+            summ = prof.summary()                          # call counts and algorithmic work per entry point
+            _lib.profiler = None
+            ts.use_cuda_graph = ts_graph
+            ts._switch = ts_switch
+            # device time per entry point: its recorded launches replayed back to back in one CUDA graph (CUDA events)
+            gemm_names = {"grappa_gemm", "grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"}     # one kernel family: one roofline entry
+            summ.setdefault("grappa_gemm", {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+            for other in ("grappa_gemm_actgrad", "grappa_gemm_ex", "grappa_gemm_bf16x3"):
+                if other in summ:
+                    extra_g = summ.pop(other)
+                    for k2 in ("calls", "ms", "flops"):
+                        summ["grappa_gemm"][k2] += extra_g[k2]
+            names = sorted(summ.keys())
+            dev_ms = {n: prof.replay_ms(gemm_names if n == "grappa_gemm" else {n}) for n in names}
+            tot = sum(dev_ms.values())
+            step_ms = ms / K
+            gm = summ["grappa_gemm"]
+            gemm_ms = dev_ms["grappa_gemm"]
+            tf = gm["flops"] / (gemm_ms * 1e-3) / 1e12
+            peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+            # fp32-accurate ceiling: a split product costs 3 MMAs; kind::f16 (bf16 planes) runs at the bf16 peak, kind::tf32 at
+            # half of it -> time floor = flops_bf16x3 / (peak / 3) + flops_3xtf32 / (peak / 6)
+            _mnk = lambda n, a: (a[0], a[1], a[2]) if n == "grappa_gemm_bf16x3" else (a[1], a[2], a[3])
+            _gflops = lambda keep: (sum(2.0 * _mnk(n, a)[0] * _mnk(n, a)[1] * _mnk(n, a)[2] for n, _, _, a in prof.records
+                                        if n == "grappa_gemm_bf16x3" and keep(n, a)),
+                                    sum(2.0 * _mnk(n, a)[0] * _mnk(n, a)[1] * _mnk(n, a)[2] for n, _, _, a in prof.records
+                                        if n in gemm_names and n != "grappa_gemm_bf16x3" and keep(n, a)))
+            def ceiling_frac(keep, t_ms):
+                fb, ft = _gflops(keep)
+                return (fb / (peak_tf / 3.0) + ft / (peak_tf / 6.0)) / 1e12 / (t_ms * 1e-3)
+            every = lambda n, a: True
+            line["roofline"] = {"kernel": {0: "sgemm_kernel", 1: "gemm_tc_kernel", 2: "gemm_bf16_kernel + gemm_tc_kernel"}[ops.MATH_MODE] +
+                                          " (grappa_gemm: all dense layers fwd+bwd, fused bias/ELU/dropout/residual epilogue)",
+                                "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                                "frac_of_fp32_accurate_ceiling": ceiling_frac(every, gemm_ms),
+                                "flops_bf16x3": _gflops(every)[0], "flops_3xtf32": _gflops(every)[1],
+                                "traffic": None, "peak_source": f"{pk_src} bf16 sustained (MEASURED_PEAKS.json)",
+                                "pipe": "fp32 FFMA (math_mode 0)" if ops.MATH_MODE == 0 else
+                                        "tcgen05, 3 MMAs per product for fp32-level accuracy: kind::f16 on bf16 hi/lo planes (forward, "
+                                        "dX; ceiling = bf16 peak / 3) and kind::tf32 (weight gradients; ceiling = bf16 peak / 6); "
+                                        "frac_of_fp32_accurate_ceiling = that time floor / measured time",
+                                "share_of_step": gemm_ms / tot, "launches_per_step": gm["calls"],
+                                "share_note": "share of the summed device time of this library's kernels; the step itself overlaps "
+                                              "kernels on parallel streams, so the sum exceeds the step time",
+                                "flops_per_step": gm["flops"], "ms_per_step": gemm_ms,
+                                "avg_launch_us": gemm_ms * 1e3 / gm["calls"],
+                                "method": "the step's recorded launches replayed back to back in a CUDA graph, CUDA events",
+                                "in_step": {"achieved": gm["flops"] / (step_ms * 1e-3) / 1e12,
+                                            "frac": gm["flops"] / (step_ms * 1e-3) / 1e12 / peak_tf,
+                                            "frac_of_fp32_accurate_ceiling": ceiling_frac(every, step_ms),
+                                            "note": "the same flops over the measured step time: inside the step the GEMMs of "
+                                                    "five streams overlap each other and the other kernels, so this aggregate "
+                                                    "rate is what the step sustains; `achieved` above is the serial replay"}}
+            # The weight-gradient GEMMs are issued on low-priority side streams with a CTA budget (un-split: 4-64 CTAs
+            # each) so that they run UNDER the activation-gradient chains; replayed alone and serially they look slow by
+            # construction.  Both classes are reported; `achieved` above is over all launches, as the contract defines it.
+            is_bg = lambda n, a: n in ("grappa_gemm", "grappa_gemm_ex", "grappa_gemm_bf16x3") and ((a[19] >> 16) & 1) == 1
+            mnk = lambda n, a: (a[0], a[1], a[2]) if n == "grappa_gemm_bf16x3" else (a[1], a[2], a[3])
+            fl = {"foreground": [0.0, 0], "background": [0.0, 0]}
+            for n, _, _, a in prof.records:
+                if n in gemm_names:
+                    c = fl["background" if is_bg(n, a) else "foreground"]
+                    c[0] += 2.0 * mnk(n, a)[0] * mnk(n, a)[1] * mnk(n, a)[2]
+                    c[1] += 1
+            for cls, keep in (("foreground", lambda n, a: not is_bg(n, a)), ("background", is_bg)):
+                ms_c = prof.replay_ms(gemm_names, keep=keep)
+                if ms_c > 0:
+                    line["roofline"][cls] = {"launches": fl[cls][1], "flops": fl[cls][0], "ms": ms_c,
+                                             "achieved": fl[cls][0] / (ms_c * 1e-3) / 1e12,
+                                             "frac_of_fp32_accurate_ceiling": ceiling_frac(keep, ms_c)}
+            line["roofline"]["class_note"] = ("foreground = GEMMs on the critical chains (forward, activation gradients); background = "
+                                              "weight-gradient GEMMs on low-priority side streams, deliberately un-split (few CTAs) so "
+                                              "that they fill idle SMs under the chains: 4.06 -> 3.93 ms per step")
+            others = {}
+            for name, label in (("grappa_energy_fwd", "energy_fwd"), ("grappa_energy_vjp", "energy_vjp"), ("grappa_gnn_attn_fwd", "gnn_attn_fwd")):
+                if name in summ and dev_ms.get(name, 0) > 0:
+                    d = summ[name]
+                    gbs = d["bytes"] / (dev_ms[name] * 1e-3) / 1e9
+                    others[label] = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                                     "us_per_call": dev_ms[name] * 1e3 / d["calls"]}
+            try:     # DRAM traffic of the dominant kernel from the committed ncu --set full capture (profiles/)
+                with open(os.path.join(ROOT, "profiles", "r02_gemm_traffic.json")) as f:
+                    tr = json.load(f)
+                line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
+                line["roofline"]["traffic_note"] = tr["note"]
+            except Exception:
+                pass
+            line["roofline_other_kernels"] = others
+            line["kernel_ms_per_step"] = {k: round(v, 4) for k, v in sorted(dev_ms.items(), key=lambda kv: -kv[1])}
+            line["kernel_ms_per_step"]["_sum_own_kernels"] = round(tot, 4)
+            line["kernel_ms_per_step"]["_step"] = round(step_ms, 4)
+        except Exception as e:        # a failed side measurement must not cost the headline numbers above
+            line.setdefault("roofline", {"error": f"kernel profile pass failed: {type(e).__name__}: {str(e)[:300]}"})
+            _lib.profiler = None
+            ts.use_cuda_graph, ts._switch = ts_graph, ts_switch
 
     # ---- side measurements on rank 0: inference (cfg 3) and energy sweep (cfg 4) ----
     if rank == 0 and world == 1 and not args.no_extras:
-        line["extra"] = extras(dev, pk)
-        line["extra"]["device_collate"] = collate_bench(ts, dev, K)
-    if world > 1:
-        torch.distributed.barrier()
+        try:
+            line["extra"] = extras(dev, pk)
+            line["extra"]["device_collate"] = collate_bench(ts, dev, K)
+        except Exception as e:
+            line.setdefault("extra", {})["error"] = f"{type(e).__name__}: {str(e)[:300]}"
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        base, _ = cpu_train_baseline(sd_cpu, g_host, steps=3, warmup=1)
-        line["cpu_baseline"] = base
+        try:
+            base, _ = cpu_train_baseline(sd_cpu, g_host, steps=3, warmup=1)
+            line["cpu_baseline"] = base
+        except Exception as e:
+            line["cpu_baseline"] = {"error": f"{type(e).__name__}: {str(e)[:300]}"}
     elif rank == 0:
         line["cpu_baseline"] = None
     if rank == 0:
-        emit(line)
+        emit(line)                       # before the last barrier: the other ranks wait there while rank 0 measures
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
