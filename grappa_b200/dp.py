@@ -54,6 +54,37 @@ def shard_of(lo: int, hi: int, rank: int, world: int) -> Tuple[int, int]:
     return lo + 4 * a, 4 * (b - a)
 
 
+def update_stages(offsets, numel: int, n_blocks: int, ffn_split_blocks=(0,)):
+    """Forward-ordered parameter stages of the staged exchange + update (train_step.TrainStep.exchange_and_update).
+
+    `offsets`: parameter name -> first element in the flat buffers, in registration order (GNN first, then the writers).
+    Returns (bounds, stage_of_mark, writer_stage, bucket_split):
+      bounds         sorted stage boundaries, stage i = [bounds[i], bounds[i+1]);
+      stage_of_mark  (block, part) -> stage whose parameters the forward reads first at that point: part 0 = the start of GNN
+                     block i >= 1, part 1 = the self-interaction weights of a block listed in `ffn_split_blocks` (only when
+                     they are the tail of the block's parameters, so that the cut leaves two contiguous ranges);
+      writer_stage   stage of the four writers (None without writers); bucket_split = its first element."""
+    names = list(offsets)
+    writers = [n for n in names if not n.startswith("gnn.")]
+    bucket_split = offsets[writers[0]] if writers else numel
+    if not all(offsets[n] >= bucket_split for n in writers):
+        raise ValueError("writer parameters must follow the GNN's")
+    marks = {}
+    for i in range(n_blocks):
+        own = sorted((offsets[n], n) for n in names if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}."))
+        if not own:
+            continue
+        if i >= 1:
+            marks[(i, 0)] = own[0][0]
+        ffn = [o for o, n in own if ".self_interaction." in n]
+        if i in ffn_split_blocks and ffn and all(".self_interaction." in n for o, n in own if o >= min(ffn)):
+            marks[(i, 1)] = min(ffn)
+    bounds = sorted(set([0] + list(marks.values()) + [bucket_split, numel]))
+    stage_of_mark = {k: bounds.index(o) for k, o in marks.items()}
+    writer_stage = bounds.index(bucket_split) if bucket_split in bounds[:-1] else None
+    return bounds, stage_of_mark, writer_stage, bucket_split
+
+
 def gather_shards_(tensors, ranges, group=None) -> None:
     """Completes every rank's copy of flat buffers whose ranges are sharded as `shard_of` says (the Adam moments under the
     fused exchange): each owner broadcasts its shard of every range.  In place; any backend."""

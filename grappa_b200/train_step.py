@@ -24,7 +24,7 @@ import torch
 
 from . import _lib, ops
 from .batching import DeviceBatch, PackedBatch
-from .dp import SwitchMemory, all_reduce_sum_, gather_shards_, shard_of
+from .dp import SwitchMemory, all_reduce_sum_, gather_shards_, shard_of, update_stages
 from .energy import Energy
 from .plan import get_plan
 
@@ -183,34 +183,17 @@ class TrainStep:
             offs = [(self.flat.offsets[n], p.numel()) for n, p in self.flat.named if n.startswith(prefix)]
             if offs:
                 self._writer_ranges[lvl] = (min(o for o, _ in offs), max(o + (k + 3) // 4 * 4 for o, k in offs))
-        first_writer = [n for n, _ in self.flat.named if not n.startswith("gnn.")]
-        self.bucket_split = self.flat.offsets[first_writer[0]] if first_writer else self.flat.numel
-        assert all(self.flat.offsets[n] >= self.bucket_split for n in first_writer), "writer parameters must follow the GNN's"
         # Staged update (world_size > 1): the parameters are exchanged + updated in FORWARD order in stages --
         # [pre_dense + GNN block 0 | block 1 | block 2 | block 3 + post_dense | the four writers].  Stage 0 runs on the compute
-        # stream; the later ones (all-reduce wait + AdamW + plane refresh) on the update stream UNDER the next step's forward,
+        # stream; the later ones (exchange + AdamW + plane refresh) on the update stream UNDER the next step's forward,
         # which waits for stage i only right before it reads that stage's parameters (external-event wait nodes in the
-        # step graph).  Exposed communication = the first stage's all-reduce.
+        # step graph).  Exposed communication = the first stage's exchange.
         # The block listed in `ffn_split_blocks` (default: block 0) is cut once more in front of its self-interaction
-        # weights (4/5 of a block's parameters), so the one all-reduce nothing can hide -- the first stage's, which the next
+        # weights (4/5 of a block's parameters), so the one exchange nothing can hide -- the first stage's, which the next
         # forward needs at once -- carries pre_dense + the attention half of block 0 only (2.3 MB instead of 10.7 MB).
-        bounds = [0]
         n_blocks = len(getattr(self.model.gnn, "blocks", []))
-        self._stage_mark = {}                       # (block, part) -> first flat offset of that stage
-        for i in range(n_blocks):
-            own = sorted((self.flat.offsets[n], n) for n, _ in self.flat.named
-                         if n.startswith(f"gnn.att_blocks.{i}.") or n.startswith(f"gnn.blocks.{i}."))
-            if not own:
-                continue
-            if i >= 1:
-                self._stage_mark[(i, 0)] = own[0][0]
-            ffn = [o for o, n in own if ".self_interaction." in n]
-            if i in ffn_split_blocks and ffn and all(".self_interaction." in n for o, n in own if o >= min(ffn)):
-                self._stage_mark[(i, 1)] = min(ffn)
-        bounds += list(self._stage_mark.values()) + [self.bucket_split, self.flat.numel]
-        self._stage_bounds = sorted(set(bounds))
-        self._stage_of_mark = {k: self._stage_bounds.index(o) for k, o in self._stage_mark.items()}
-        self._writer_stage = self._stage_bounds.index(self.bucket_split) if self.bucket_split in self._stage_bounds[:-1] else None
+        self._stage_bounds, self._stage_of_mark, self._writer_stage, self.bucket_split = update_stages(
+            self.flat.offsets, self.flat.numel, n_blocks, tuple(ffn_split_blocks))
         for _ in range(len(self._stage_bounds) - 1):
             ev = torch.cuda.Event(external=True)
             ev.record(torch.cuda.current_stream(self.device))

@@ -160,3 +160,41 @@ def test_sharded_update_equals_replicated_update_world2(tmp_path):
     port = _free_port()
     mp.spawn(_shard_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert sorted(os.listdir(tmp_path)) == ["ok0", "ok1"]
+
+
+def test_update_stages_follow_the_forward_order_of_the_default_model():
+    """Host logic of the staged exchange (train_step.TrainStep): contiguous stages in the order the forward reads the
+    parameters, block 0 cut in front of its self-interaction weights, the four writers last."""
+    from grappa_b200.dp import update_stages
+    from grappa_b200.model import GrappaModel
+    from grappa_b200.train_step import FlatParameters
+    model = GrappaModel.from_default_config()
+    flat = FlatParameters(model, "cpu")
+    n_blocks = len(model.gnn.blocks)
+    bounds, marks, writer_stage, split = update_stages(flat.offsets, flat.numel, n_blocks, (0,))
+    assert bounds[0] == 0 and bounds[-1] == flat.numel and bounds == sorted(set(bounds)) and all(b % 4 == 0 for b in bounds)
+    assert len(bounds) - 1 == 6 and writer_stage == 5 and bounds[5] == split
+    assert marks == {(0, 1): 1, (1, 0): 2, (2, 0): 3, (3, 0): 4}
+    stage_of = lambda name: max(i for i in range(len(bounds) - 1) if bounds[i] <= flat.offsets[name])
+    for name, p in flat.named:                                   # no parameter straddles a boundary
+        s = stage_of(name)
+        assert flat.offsets[name] + p.numel() <= bounds[s + 1], name
+        if name.startswith("gnn.pre_dense"):
+            assert s == 0
+        elif name.startswith("gnn.att_blocks.0."):
+            assert s == (1 if ".self_interaction." in name else 0), name
+        elif name.startswith("gnn.att_blocks."):
+            assert s == int(name.split(".")[2]) + 1, name
+        elif name.startswith("gnn.post_dense"):
+            assert s == 4
+        else:
+            assert s == 5, name
+    assert bounds[1] == flat.offsets["gnn.att_blocks.0.self_interaction.0.weight"]
+    assert 4 * bounds[1] < 2.5e6 < 10e6 < 4 * bounds[2]          # first stage 2.3 MB instead of 10.7 MB
+    # without the extra cut: the five stages of the coarser scheme; every block cut: nine
+    assert len(update_stages(flat.offsets, flat.numel, n_blocks, ())[0]) - 1 == 5
+    assert len(update_stages(flat.offsets, flat.numel, n_blocks, (0, 1, 2, 3))[0]) - 1 == 9
+    # a model without writers has no writer stage
+    gnn_only = {n: o for n, o in flat.offsets.items() if n.startswith("gnn.")}
+    b2, _, ws2, split2 = update_stages(gnn_only, split, n_blocks, (0,))
+    assert ws2 is None and split2 == split and b2[-1] == split
