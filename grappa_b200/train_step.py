@@ -153,18 +153,17 @@ class TrainStep:
         # STATUS (round 1): the stream choreography is verified on one GPU with a stand-in exchange
         # (tests/test_gpu_model.py::test_bucketed_gradient_exchange_choreography), but with real NCCL collectives the
         # 2-GPU run hung (twice, issued from the autograd thread and from the calling thread), so it is OFF by default and
-        # refused for world_size > 1 until that is understood; the default is one all-reduce after backward (measured
-        # exposed cost: 0.19 ms at N = 2, 0.38 ms at N = 8 of a 5.2 ms step).
+        # refused for world_size > 1 (NCCL collectives captured into a CUDA graph hang on this stack: scratch/nccl_graph_probe.py).
+        # Round 2 replaced it by the forward-ordered staged exchange below (split_update), fused with AdamW over NVSwitch memory.
         self.overlap_comm = bool(overlap_comm)
         if self.overlap_comm and world_size > 1:
             raise NotImplementedError("overlap_comm with NCCL hung on 2 x B200 in round 1; use the default single all-reduce")
         self._comm_stream = torch.cuda.Stream(device=self.device)
         self._copy_stream = torch.cuda.Stream(device=self.device)        # input prefetch (H2D of the next step's batch)
-        # Split update: the GNN's parameters are exchanged + updated first, on the compute stream; the writers' (second
-        # half of the flat buffers) on an update stream, UNDER the next step's GNN forward, which does not read them.
-        # The step's graph holds an external-event wait node between the GNN forward and the writers.
-        # Measured: 2 GPUs 4.26 -> 4.20 ms; on one GPU there is only half an AdamW to hide and the extra launch + event cost
-        # as much (4.07 both ways), hence the default: on for world_size > 1.
+        # Split (staged) update: the first parameter stage is exchanged + updated on the compute stream, the later ones on an
+        # update stream UNDER the next step's forward, which reads them later (stage list below; external-event wait nodes
+        # in the step's graph).  On one GPU there is only an AdamW to hide and the wait nodes cost as much (3.237 vs 3.224 ms),
+        # hence the default: on for world_size > 1.
         self.split_update = (world_size > 1) if split_update is None else bool(split_update)
         self._upd_stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._writers_ready = torch.cuda.Event(external=True)
