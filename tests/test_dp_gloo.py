@@ -198,3 +198,12 @@ def test_update_stages_follow_the_forward_order_of_the_default_model():
     gnn_only = {n: o for n, o in flat.offsets.items() if n.startswith("gnn.")}
     b2, _, ws2, split2 = update_stages(gnn_only, split, n_blocks, (0,))
     assert ws2 is None and split2 == split and b2[-1] == split
+
+
+def test_switch_exchange_is_only_offered_for_multi_gpu_cuda_jobs(monkeypatch):
+    from grappa_b200.dp import SwitchMemory
+    assert SwitchMemory.available(1) is False                     # one rank: nothing to exchange
+    monkeypatch.setenv("GRAPPA_DP_SWITCH", "0")
+    assert SwitchMemory.available(8) is False                     # explicit opt-out -> NCCL all-reduce path
+    monkeypatch.delenv("GRAPPA_DP_SWITCH")
+    assert SwitchMemory.available(8) is torch.cuda.is_available() # needs CUDA devices (False on the CPU test box)
